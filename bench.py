@@ -1,0 +1,482 @@
+#!/usr/bin/env python3
+"""bench.py -- the measurement contract for the cux operator hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl ours|reference]
+    torchrun ... bench.py --gpus N ...           (one rank per GPU, NCCL)
+
+Prints ONE JSON line.  The default workload is BASELINE.json configs[1]: the cux `dot`
+operator, fp32, N = 2^28 elements per GPU (2 x 1 GiB read per GPU, far larger than the 126 MB L2).
+A step is one pass of the hot path: the dot kernel over this rank's vectors and, at N > 1, one NCCL
+all-reduce of the per-GPU partial (north_star: "a per-GPU partial and then a single NCCL allreduce").
+  value  = bytes all ranks read / max-over-ranks device time   [GB/s], inputs resident in HBM
+  e2e    = the same metric through the host-buffer C-ABI call (cuxb_dot_f32_host): pinned host
+           vectors are copied host->device every step and the scalar is read back
+  roofline / cpu_baseline / clocks / gpu_launches: see the task contract and DESIGN.md.
+Other workloads (--workload sum|nrm2|scan|sgemm|hgemm|linear_s8) time the remaining BASELINE
+configs; at N=1 a short pass over each is reported under "also".
+
+--impl reference times the reference's own CPU implementation of the same workload (oracle/_ref
+when built, else the oracle port) on the host cores; that is the only product-side use of oracle/.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_DOT = 1 << 28
+N_SCAN = 1 << 30
+SGEMM_N = 8192
+HGEMM_N = 16384
+LIN8_N = 8192
+FP32_FFMA_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4: 148 SMs x 128 lanes x 2 x clocks.max.sm
+INT8_NOMINAL_TOPS = 4500.0
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {"hbm_gbs": p["hbm_gbs"], "tensor_tflops": p["bf16_tflops"],
+                "tensor_tflops_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tensor_tflops": 1590.0, "tensor_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (recipe in B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons, power = [], [], set(), []
+        for ts, line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                if t0 - 0.05 <= ts <= t1 + 0.15:
+                    sm.append(float(f[1]))
+                    power.append(float(f[3]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            if t0 - 0.05 <= ts <= t1 + 0.15:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------- workloads (GPU)
+class Workload:
+    """name, per-rank algorithmic work per step, the step itself (device-resident inputs)."""
+
+    def __init__(self, torch, ctx, world):
+        self.torch, self.ctx, self.world = torch, ctx, world
+
+    def gen_int(self, shape, lo, hi, dtype, seed):
+        g = self.torch.Generator(device="cuda")
+        g.manual_seed(seed)
+        return self.torch.randint(lo, hi + 1, shape, device="cuda", generator=g, dtype=self.torch.int32).to(dtype)
+
+
+def make_workload(name, torch, ctx, world, rank, dist):
+    from hpc_b200 import capi
+    W = Workload(torch, ctx, world)
+    stream = lambda: torch.cuda.current_stream().cuda_stream
+    seed = 20240607 + 17 * rank
+    if name in ("dot", "sum", "nrm2"):
+        n = N_DOT
+        a = W.gen_int((n,), -2, 2, torch.float32, seed)        # cux fill, demo.cpp:30
+        b = W.gen_int((n,), -2, 2, torch.float32, seed + 1) if name == "dot" else None
+        res = torch.zeros(1, device="cuda")
+        fn = {"dot": lambda: ctx.dot_f32(n, a.data_ptr(), b.data_ptr(), res.data_ptr(), stream()),
+              "sum": lambda: ctx.sum_f32(n, a.data_ptr(), res.data_ptr(), stream()),
+              "nrm2": lambda: ctx.nrm2_f32(n, a.data_ptr(), res.data_ptr(), stream())}[name]
+        sq = torch.zeros(1, device="cuda")
+
+        def step():
+            fn()
+            if world > 1:
+                if name == "nrm2":   # combine squared norms, then sqrt
+                    torch.mul(res, res, out=sq)
+                    dist.all_reduce(sq)
+                    torch.sqrt(sq, out=res)
+                else:
+                    dist.all_reduce(res)
+        W.kernel = fn
+        W.step = step
+        W.units = (8 if name == "dot" else 4) * n
+        W.unit, W.bound, W.dtype = "GB/s", "hbm", "f32"
+        W.desc = "cux %s fp32 N=2^28 per GPU (configs[1]); inputs %d MiB per GPU > L2, no flush needed" % (
+            name, W.units >> 20)
+        W.metric = "reduce HBM GB/s (fp32 %s, N=2^28 per GPU)" % ("dot-product" if name == "dot" else name)
+        W.result = res
+        W.launches_per_step = 1
+        W.host_inputs = lambda: [a, b] if b is not None else [a]
+    elif name == "scan":
+        n = N_SCAN
+        x = W.gen_int((n,), -2, 2, torch.int32, seed)
+        out = torch.empty_like(x)
+        tot = torch.zeros(1, dtype=torch.int32, device="cuda")
+        if world == 1:
+            fn = lambda: ctx.scan_i32(n, x.data_ptr(), out.data_ptr(), 0, stream())
+            step = fn
+            W.launches_per_step = 1
+        else:
+            gathered = torch.zeros(world, dtype=torch.int32, device="cuda")
+            fn = lambda: ctx.scan_i32(n, x.data_ptr(), out.data_ptr(), 0, stream())
+
+            def step():
+                # phase 1: local total; exchange; phase 2: scan seeded with the exclusive offset
+                ctx.sum_i32(n, x.data_ptr(), tot.data_ptr(), stream())
+                dist.all_gather_into_tensor(gathered, tot)
+                seed_val = int(gathered[:rank].sum().item()) if rank else 0
+                seed_val = (seed_val + 2 ** 31) % 2 ** 32 - 2 ** 31
+                ctx.scan_i32(n, x.data_ptr(), out.data_ptr(), seed_val, stream())
+            W.launches_per_step = 2
+        W.kernel, W.step = fn, step
+        W.units = 8 * n
+        W.unit, W.bound, W.dtype = "GB/s", "hbm", "i32"
+        W.desc = "int32 inclusive scan N=2^30 per GPU (configs[4]); 8 GiB moved per GPU > L2"
+        W.metric = "scan HBM GB/s (int32 inclusive prefix scan, N=2^30 per GPU)"
+        W.result = out[-1:]
+    elif name in ("sgemm", "hgemm", "linear_s8"):
+        if name == "sgemm":
+            n = SGEMM_N
+            A = W.gen_int((n, n), -2, 5, torch.float32, seed)
+            B = W.gen_int((n, n), -2, 5, torch.float32, 20240607 + 99)   # B identical on every rank
+            C = torch.zeros((n, n), device="cuda")
+            fn = lambda: ctx.sgemm_f32(n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n, stream())
+            W.dtype, W.peak_kind = "f32", "ffma"
+            W.desc = "fp32 SGEMM %d^3 per GPU on CUDA cores (configs[2]); rows of C sharded, B replicated" % n
+            W.metric = "GEMM TFLOP/s (fp32 SGEMM 8192^3 per GPU, CUDA cores)"
+        elif name == "hgemm":
+            n = HGEMM_N
+            A = W.gen_int((n, n), -10, 9, torch.float16, seed)
+            B = W.gen_int((n, n), -10, 9, torch.float16, 20240607 + 99)
+            C = torch.zeros((n, n), dtype=torch.float16, device="cuda")
+            fn = lambda: ctx.hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n,
+                                       capi.FLOAT16, stream())
+            W.dtype, W.peak_kind = "f16 (fp32 accumulate)", "tensor"
+            W.desc = "fp16 GEMM %d^3 per GPU, fp32 accumulate, tcgen05/TMEM (configs[3]); rows of C sharded, B replicated" % n
+            W.metric = "GEMM TFLOP/s (fp16 GEMM 16384^3 per GPU, fp32 accumulate, tcgen05)"
+        else:
+            n = LIN8_N
+            A = W.gen_int((n, n), 0, 16, torch.int8, seed)
+            B = W.gen_int((n, n), -8, 8, torch.int8, 20240607 + 99)
+            C = torch.zeros((n, n), dtype=torch.int32, device="cuda")
+            fn = lambda: ctx.linear_s8(n, n, n, A.data_ptr(), B.data_ptr(), C.data_ptr(), stream())
+            W.dtype, W.peak_kind = "s8 (int32 accumulate)", "tensor_int8"
+            W.desc = "int8 linear %d^3 per GPU, int32 accumulate, tcgen05 kind::i8 (configs[4])" % n
+            W.metric = "GEMM TOP/s (int8 linear 8192^3 per GPU, int32 accumulate)"
+        W.kernel = W.step = fn
+        W.units = 2 * n * n * n
+        W.unit = "TOP/s" if name == "linear_s8" else "TFLOP/s"
+        W.bound = "tensor" if name != "sgemm" else "ffma"
+        W.result = C[-1, -1:]
+        W.launches_per_step = 1
+    else:
+        raise SystemExit("unknown workload " + name)
+    W.name = name
+    return W
+
+
+def time_steps(torch, fn, steps, warmup, dist=None):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    t1 = time.time()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        torch.cuda.synchronize()
+        ms = float(t[0])
+    return ms, t0, t1
+
+
+def rate(units, ms, unit):
+    per_s = units / (ms * 1e-3)
+    return per_s / 1e9 if unit == "GB/s" else per_s / 1e12
+
+
+def peak_for(W, peaks):
+    if W.bound == "hbm":
+        return peaks["hbm_gbs"], "GB/s", "MEASURED_PEAKS.json hbm_gbs (%s)" % peaks["source"]
+    if W.name == "sgemm":
+        return FP32_FFMA_PEAK_TFLOPS, "TFLOP/s", "FP32 FFMA 148 SM x 128 x 2 x 1.965 GHz (nominal; no measured FFMA peak)"
+    if W.name == "linear_s8":
+        return 2 * peaks["tensor_tflops"], "TOP/s", "2 x MEASURED_PEAKS.json bf16_tflops (int8 = 2x bf16 rate; %s)" % peaks["source"]
+    return peaks["tensor_tflops"], "TFLOP/s", "MEASURED_PEAKS.json bf16_tflops burst (%s)" % peaks["source"]
+
+
+# --------------------------------------------------------------------------- CPU reference arm
+def cpu_dot_reference(n, seconds_budget, seed=20240607):
+    """DotHostV0 (0-frameworks/cux/src/operator/dot_product.cpp:7-13) on this host, single thread
+    (the reference's dot has no parallel variant inside cux).  Returns (GB/s, kind, passes)."""
+    import oracle
+    rng = np.random.default_rng(seed)
+    a = rng.integers(-2, 3, size=n).astype(np.float32)
+    b = rng.integers(-2, 3, size=n).astype(np.float32)
+    out = np.zeros(1, np.float32)
+    R = oracle.ref()
+    if R is not None:
+        kind, f = "reference", lambda: R.ref_cux_dot_v0(n, a, b, out)
+    else:
+        L = oracle.lib()
+        kind, f = "port", lambda: L.orc_dot_f32(n, a, b, out)
+    f()
+    times = []
+    t_end = time.time() + seconds_budget
+    while True:
+        t0 = time.perf_counter()
+        f()
+        times.append(time.perf_counter() - t0)
+        if time.time() > t_end or len(times) >= 64:
+            break
+    return times, kind, float(out[0])
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    if args.workload != "dot":
+        print(json.dumps({"impl": "reference", "unavailable": "reference arm implemented for the default dot workload only"}))
+        return
+    n = N_DOT
+    import oracle
+    rng = np.random.default_rng(20240607)
+    a = rng.integers(-2, 3, size=n).astype(np.float32)
+    b = rng.integers(-2, 3, size=n).astype(np.float32)
+    out = np.zeros(1, np.float32)
+    R = oracle.ref()
+    if R is not None:
+        kind, f = "reference", lambda: R.ref_cux_dot_v0(n, a, b, out)
+    else:
+        kind, f = "port", lambda: oracle.lib().orc_dot_f32(n, a, b, out)
+    for _ in range(args.warmup):
+        f()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        f()
+    dt = time.perf_counter() - t0
+    ms = dt * 1e3 / args.steps
+    v = 8 * n / (ms * 1e-3) / 1e9
+    line = {
+        "impl": "reference", "metric": "reduce HBM GB/s (fp32 dot-product, N=2^28 per GPU)", "value": v, "unit": "GB/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "cux dot fp32 N=2^28 (configs[1]) on the host CPU: DotHostV0, single thread (cux has no parallel dot)"},
+        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": 1, "kind": kind,
+                         "sample": "full N=2^28 vectors (2 GiB read) per step"},
+        "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------- main (GPU arm)
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="dot", choices=["dot", "sum", "nrm2", "scan", "sgemm", "hgemm", "linear_s8"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-also", action="store_true", help="skip the short passes over the other workloads")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import torch
+    from hpc_b200 import capi
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = capi.Context(local)
+    peaks = load_peaks()
+    W = make_workload(args.workload, torch, ctx, world, rank, dist)
+    warmup = max(args.warmup, 3)
+
+    # ---- device-resident timing (value)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    l0 = capi.launch_count()
+    ms_total, t0, t1 = time_steps(torch, W.step, args.steps, warmup, dist)
+    launches = (capi.launch_count() - l0) - warmup * W.launches_per_step
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    ms_step = ms_total / args.steps
+    value = rate(W.units * world, ms_step, W.unit)
+
+    # ---- the dominant kernel alone, on the launching stream (roofline.achieved)
+    ms_k, _, _ = time_steps(torch, W.kernel, args.steps, 3, None)
+    ms_kernel = ms_k / args.steps
+    achieved = rate(W.units, ms_kernel, W.unit)
+    peak, punit, pnote = peak_for(W, peaks)
+    roofline = {"bound": "hbm" if W.bound == "hbm" else "tensor" if W.bound == "tensor" else "ffma",
+                "achieved": achieved, "peak": peak, "unit": punit, "frac": achieved / peak,
+                "traffic": None, "kernel_ms": ms_kernel, "peak_source": pnote,
+                "algorithmic_units_per_launch": W.units}
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        roofline["traffic"] = json.load(open(tpath)).get(W.name)
+
+    # ---- end to end through the host-buffer C ABI (pinned host memory, H2D + kernel + D2H per step)
+    e2e = None
+    if args.workload == "dot":
+        n = N_DOT
+        ha = torch.empty(n, dtype=torch.float32, pin_memory=True)
+        hb = torch.empty(n, dtype=torch.float32, pin_memory=True)
+        ins = W.host_inputs()
+        ha.copy_(ins[0])
+        hb.copy_(ins[1])
+        hres = torch.zeros(1, dtype=torch.float32, pin_memory=True)
+        part = torch.zeros(1, device="cuda")
+
+        def e2e_step():
+            ctx.dot_f32_host(n, ha.data_ptr(), hb.data_ptr(), hres.data_ptr())
+            if world > 1:
+                part.copy_(hres, non_blocking=True)
+                dist.all_reduce(part)
+                hres.copy_(part)
+        e2e_steps = max(3, min(args.steps, 10))
+        t_w0 = time.perf_counter()
+        for _ in range(2):
+            e2e_step()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        t_a = time.perf_counter()
+        for _ in range(e2e_steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t_a], device="cuda")
+        if dist is not None:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(dt[0]) * 1e3 / e2e_steps
+        e2e = {"value": rate(W.units * world, e2e_ms, "GB/s"), "unit": "GB/s", "h2d_bytes_per_step": 8 * n,
+               "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "api": "cuxb_dot_f32_host (pinned host vectors; host wall clock around the blocking call)",
+               "result": float(hres[0]), "device_result": float(W.result[0])}
+
+    # ---- short passes over the other configs (N=1 only)
+    also = {}
+    if world == 1 and not args.no_also:
+        device_result = float(W.result[0])
+        W = None
+        torch.cuda.empty_cache()
+        for name in ["sum", "nrm2", "scan", "sgemm", "hgemm", "linear_s8"]:
+            if name == args.workload:
+                continue
+            try:
+                w2 = make_workload(name, torch, ctx, 1, 0, None)
+                ms2, _, _ = time_steps(torch, w2.kernel, 10 if w2.bound == "hbm" else 5, 3, None)
+                ms2 /= (10 if w2.bound == "hbm" else 5)
+                ach = rate(w2.units, ms2, w2.unit)
+                pk, pu, pn = peak_for(w2, peaks)
+                also[name] = {"value": ach, "unit": w2.unit, "ms": ms2, "peak": pk, "frac": ach / pk,
+                              "peak_source": pn, "workload": w2.desc}
+                del w2
+                torch.cuda.empty_cache()
+            except Exception as ex:  # reported, not hidden
+                also[name] = {"error": str(ex)[:300]}
+
+    # ---- CPU baseline leg (rank 0, N=1): DotHostV0 on the host cores
+    cpu = None
+    if world == 1 and rank == 0 and not args.no_cpu and args.workload == "dot":
+        times, kind, _ = cpu_dot_reference(N_DOT, 10.0)
+        best = float(np.median(times))
+        cpu = {"value": 8 * N_DOT / best / 1e9, "unit": "GB/s", "cores": 1, "kind": kind,
+               "sample": "DotHostV0 over the full N=2^28 vectors, %d passes (median), single thread as in cux" % len(times)}
+
+    if rank == 0:
+        wl = make_desc(args.workload)
+        line = {
+            "metric": wl["metric"], "value": value, "unit": wl["unit"], "n_gpus": world, "steps": args.steps,
+            "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
+            "config": {"workload": wl["desc"], "l2": "inputs larger than L2 (no flush needed)" if wl["hbm"] else
+                       "GEMM operands exceed L2; no flush", "parallelism": "one rank per GPU, per-GPU partial + one NCCL all-reduce"
+                       if wl["hbm"] else "rows of C sharded per GPU, B replicated"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "also": also,
+        }
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def make_desc(name):
+    d = {
+        "dot": ("reduce HBM GB/s (fp32 dot-product, N=2^28 per GPU)", "GB/s", "f32",
+                "cux dot fp32 N=2^28 per GPU (configs[1]), integer-valued fill [-2,2] as cux's demo", True),
+        "sum": ("reduce HBM GB/s (fp32 sum, N=2^28 per GPU)", "GB/s", "f32", "fp32 sum-reduce N=2^28 per GPU (configs[1])", True),
+        "nrm2": ("reduce HBM GB/s (fp32 nrm2, N=2^28 per GPU)", "GB/s", "f32", "cux nrm2 fp32 N=2^28 per GPU", True),
+        "scan": ("scan HBM GB/s (int32 inclusive scan, N=2^30 per GPU)", "GB/s", "i32", "int32 prefix scan N=2^30 per GPU (configs[4])", True),
+        "sgemm": ("GEMM TFLOP/s (fp32 SGEMM 8192^3 per GPU, CUDA cores)", "TFLOP/s", "f32", "fp32 SGEMM 8192^3 per GPU (configs[2])", False),
+        "hgemm": ("GEMM TFLOP/s (fp16 GEMM 16384^3 per GPU, fp32 accumulate, tcgen05)", "TFLOP/s", "f16",
+                  "fp16 GEMM 16384^3 per GPU, fp32 accumulate (configs[3])", False),
+        "linear_s8": ("GEMM TOP/s (int8 linear 8192^3 per GPU)", "TOP/s", "s8", "int8 linear 8192^3 per GPU (configs[4])", False),
+    }[name]
+    return {"metric": d[0], "unit": d[1], "dtype": d[2], "desc": d[3], "hbm": d[4]}
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,205 @@
+"""ctypes binding of libcuxb.so (include/cuxb.h).
+
+Python is only the test/bench driver: this module adds nothing but argument
+marshalling.  There is no fallback -- if the CUDA library is missing or a call
+fails, a CuxbError is raised.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcuxb.so")
+
+FLOAT32, INT32, FLOAT16, INT8, BFLOAT16 = 0, 1, 2, 3, 4
+
+
+class CuxbError(RuntimeError):
+    pass
+
+
+_vp, _ll, _i, _f, _sz = C.c_void_p, C.c_longlong, C.c_int, C.c_float, C.c_size_t
+
+# name -> (argtypes, restype).  Every symbol declared in include/cuxb.h is listed here;
+# tests/test_abi.py checks the header against this table and the .so.
+SIGNATURES = {
+    "cuxb_ctx_create": ([_i, C.POINTER(_vp)], _i),
+    "cuxb_ctx_destroy": ([_vp], _i),
+    "cuxb_ctx_device": ([_vp], _i),
+    "cuxb_ctx_sm_count": ([_vp], _i),
+    "cuxb_last_error_string": ([], C.c_char_p),
+    "cuxb_version": ([], C.c_char_p),
+    "cuxb_launch_count": ([], _ll),
+    "cuxb_malloc": ([C.POINTER(_vp), _sz], _i),
+    "cuxb_free": ([_vp], _i),
+    "cuxb_malloc_host": ([C.POINTER(_vp), _sz], _i),
+    "cuxb_free_host": ([_vp], _i),
+    "cuxb_memcpy_h2d": ([_vp, _vp, _sz, _vp], _i),
+    "cuxb_memcpy_d2h": ([_vp, _vp, _sz, _vp], _i),
+    "cuxb_memcpy_d2d": ([_vp, _vp, _sz, _vp], _i),
+    "cuxb_memset": ([_vp, _i, _sz, _vp], _i),
+    "cuxb_set_device": ([_i], _i),
+    "cuxb_device_count": ([C.POINTER(_i)], _i),
+    "cuxb_device_sync": ([], _i),
+    "cuxb_device_name": ([_i, C.c_char_p, _sz], _i),
+    "cuxb_stream_create": ([C.POINTER(_vp)], _i),
+    "cuxb_stream_destroy": ([_vp], _i),
+    "cuxb_stream_sync": ([_vp], _i),
+    "cuxb_event_create": ([C.POINTER(_vp)], _i),
+    "cuxb_event_destroy": ([_vp], _i),
+    "cuxb_event_record": ([_vp, _vp], _i),
+    "cuxb_event_sync": ([_vp], _i),
+    "cuxb_event_elapsed_ms": ([_vp, _vp, C.POINTER(_f)], _i),
+    "cuxb_dot_f32": ([_vp, _vp, _ll, _vp, _vp, _vp], _i),
+    "cuxb_sum_f32": ([_vp, _vp, _ll, _vp, _vp], _i),
+    "cuxb_nrm2_f32": ([_vp, _vp, _ll, _vp, _vp], _i),
+    "cuxb_sum_i32": ([_vp, _vp, _ll, _vp, _vp], _i),
+    "cuxb_scan_i32": ([_vp, _vp, _ll, _vp, _vp, C.c_int32], _i),
+    "cuxb_scan_f32": ([_vp, _vp, _ll, _vp, _vp, _f], _i),
+    "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
+    "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
+    "cuxb_linear_s8_s32": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp], _i),
+    "cuxb_linear_bf16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i], _i),
+    "cuxb_linear_f16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i], _i),
+    "cuxb_convert": ([_vp, _vp, _ll, _vp, _i, _vp, _i], _i),
+    "cuxb_dot_f32_host": ([_vp, _ll, _vp, _vp, _vp], _i),
+    "cuxb_sum_f32_host": ([_vp, _ll, _vp, _vp], _i),
+    "cuxb_nrm2_f32_host": ([_vp, _ll, _vp, _vp], _i),
+    "cuxb_scan_i32_host": ([_vp, _ll, _vp, _vp, C.c_int32], _i),
+    "cuxb_sgemm_f32_host": ([_vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
+    "cuxb_hgemm_f16_f32acc_host": ([_vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
+    "cuxb_linear_s8_s32_host": ([_vp, _i, _i, _i, _vp, _vp, _vp], _i),
+    "cuxb_kernel_occupancy": ([_vp, C.c_char_p, C.POINTER(_i), C.POINTER(C.c_double), C.POINTER(_i),
+                               C.POINTER(_i)], _i),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libcuxb.so and attach prototypes.  Raises if the library is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CuxbError("%s is missing: run `python -m hpc_b200.build` (there is no CPU fallback)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    for name, (args, res) in SIGNATURES.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = res
+    try:
+        L.cuxb_debug_set_cta_group.argtypes = [_i]
+        L.cuxb_debug_set_cta_group.restype = _i
+    except AttributeError:
+        pass
+    _lib = L
+    return L
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise CuxbError("%s failed with code %d: %s" % (what or "cuxb call", rc,
+                                                        lib().cuxb_last_error_string().decode()))
+
+
+class Context:
+    """cuxb_ctx wrapper: per-device workspace; one per device (and per concurrent stream)."""
+
+    def __init__(self, device=0):
+        self._h = _vp()
+        check(lib().cuxb_ctx_create(device, C.byref(self._h)), "cuxb_ctx_create")
+        self.device = device
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def sm_count(self):
+        return lib().cuxb_ctx_sm_count(self._h)
+
+    def close(self):
+        if self._h:
+            lib().cuxb_ctx_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- device-pointer entry points (ptr arguments are ints: tensor.data_ptr()) ---
+    def dot_f32(self, n, a, b, res, stream=0):
+        check(lib().cuxb_dot_f32(self._h, stream, n, a, b, res), "cuxb_dot_f32")
+
+    def sum_f32(self, n, x, res, stream=0):
+        check(lib().cuxb_sum_f32(self._h, stream, n, x, res), "cuxb_sum_f32")
+
+    def nrm2_f32(self, n, x, res, stream=0):
+        check(lib().cuxb_nrm2_f32(self._h, stream, n, x, res), "cuxb_nrm2_f32")
+
+    def sum_i32(self, n, x, res, stream=0):
+        check(lib().cuxb_sum_i32(self._h, stream, n, x, res), "cuxb_sum_i32")
+
+    def scan_i32(self, n, src, dst, seed=0, stream=0):
+        check(lib().cuxb_scan_i32(self._h, stream, n, src, dst, seed), "cuxb_scan_i32")
+
+    def scan_f32(self, n, src, dst, seed=0.0, stream=0):
+        check(lib().cuxb_scan_f32(self._h, stream, n, src, dst, seed), "cuxb_scan_f32")
+
+    def sgemm_f32(self, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc, stream=0):
+        check(lib().cuxb_sgemm_f32(self._h, stream, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc),
+              "cuxb_sgemm_f32")
+
+    def hgemm_f16(self, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc, c_dtype=FLOAT16, stream=0):
+        check(lib().cuxb_hgemm_f16_f32acc(self._h, stream, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc,
+                                          c_dtype), "cuxb_hgemm_f16_f32acc")
+
+    def linear_s8(self, M, N, K, A, Bt, Cp, stream=0):
+        check(lib().cuxb_linear_s8_s32(self._h, stream, M, N, K, A, Bt, Cp), "cuxb_linear_s8_s32")
+
+    def linear_bf16(self, M, N, K, A, Bt, Cp, c_dtype=BFLOAT16, stream=0):
+        check(lib().cuxb_linear_bf16_f32acc(self._h, stream, M, N, K, A, Bt, Cp, c_dtype),
+              "cuxb_linear_bf16_f32acc")
+
+    def linear_f16(self, M, N, K, A, Bt, Cp, c_dtype=FLOAT16, stream=0):
+        check(lib().cuxb_linear_f16_f32acc(self._h, stream, M, N, K, A, Bt, Cp, c_dtype),
+              "cuxb_linear_f16_f32acc")
+
+    def convert(self, n, src, src_dtype, dst, dst_dtype, stream=0):
+        check(lib().cuxb_convert(self._h, stream, n, src, src_dtype, dst, dst_dtype), "cuxb_convert")
+
+    def occupancy(self, kernel):
+        ab, occ, th, sm = _i(), C.c_double(), _i(), _i()
+        check(lib().cuxb_kernel_occupancy(self._h, kernel.encode(), C.byref(ab), C.byref(occ), C.byref(th),
+                                          C.byref(sm)), "cuxb_kernel_occupancy")
+        return ab.value, occ.value, th.value, sm.value
+
+    # --- host-buffer entry points (numpy arrays or raw host pointers) ---
+    def dot_f32_host(self, n, a_ptr, b_ptr, res_ptr):
+        check(lib().cuxb_dot_f32_host(self._h, n, a_ptr, b_ptr, res_ptr), "cuxb_dot_f32_host")
+
+    def sum_f32_host(self, n, x_ptr, res_ptr):
+        check(lib().cuxb_sum_f32_host(self._h, n, x_ptr, res_ptr), "cuxb_sum_f32_host")
+
+    def nrm2_f32_host(self, n, x_ptr, res_ptr):
+        check(lib().cuxb_nrm2_f32_host(self._h, n, x_ptr, res_ptr), "cuxb_nrm2_f32_host")
+
+    def scan_i32_host(self, n, in_ptr, out_ptr, seed=0):
+        check(lib().cuxb_scan_i32_host(self._h, n, in_ptr, out_ptr, seed), "cuxb_scan_i32_host")
+
+    def sgemm_f32_host(self, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc):
+        check(lib().cuxb_sgemm_f32_host(self._h, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc),
+              "cuxb_sgemm_f32_host")
+
+    def hgemm_f16_host(self, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc, c_dtype=FLOAT16):
+        check(lib().cuxb_hgemm_f16_f32acc_host(self._h, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc, c_dtype),
+              "cuxb_hgemm_f16_f32acc_host")
+
+    def linear_s8_host(self, M, N, K, A, Bt, Cp):
+        check(lib().cuxb_linear_s8_s32_host(self._h, M, N, K, A, Bt, Cp), "cuxb_linear_s8_s32_host")
+
+
+def launch_count():
+    return lib().cuxb_launch_count()

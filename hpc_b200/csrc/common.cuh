@@ -1,0 +1,90 @@
+// common.cuh -- shared internals of libcuxb.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <atomic>
+#include <mutex>
+
+#include "../../include/cuxb.h"
+
+#define CUXB_API extern "C" __attribute__((visibility("default")))
+
+namespace cuxb {
+
+void set_error(const char *fmt, ...);
+extern std::atomic<long long> g_launches;
+
+// Evaluate a CUDA runtime call; on failure record the message and return the code.
+#define CUXB_CUDA(expr)                                                                   \
+  do {                                                                                    \
+    cudaError_t e__ = (expr);                                                             \
+    if (e__ != cudaSuccess) {                                                             \
+      ::cuxb::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, \
+                        __LINE__);                                                        \
+      return (int)e__;                                                                    \
+    }                                                                                     \
+  } while (0)
+
+#define CUXB_REQUIRE(cond, code, ...)  \
+  do {                                 \
+    if (!(cond)) {                     \
+      ::cuxb::set_error(__VA_ARGS__);  \
+      return (code);                   \
+    }                                  \
+  } while (0)
+
+// Called after every <<< >>> / cudaLaunchKernelEx.
+#define CUXB_LAUNCHED()                       \
+  do {                                        \
+    ::cuxb::g_launches.fetch_add(1);          \
+    CUXB_CUDA(cudaGetLastError());            \
+  } while (0)
+
+static inline long long div_up(long long a, long long b) { return (a + b - 1) / b; }
+
+// Scan tile-state capacity: one 64-bit word per tile.
+constexpr int kScanTileElems = 4096;                 // 256 threads x 16 ints
+constexpr long long kScanMaxTiles = (1ll << 31) / kScanTileElems;  // n < 2^31 (cux uses int lengths)
+constexpr int kReduceMaxBlocks = 2048;
+
+struct TmaCacheEntry {
+  const void *base;
+  uint64_t dims[2];
+  uint64_t stride1;
+  uint32_t box[2];
+  int dtype_bytes;
+  int swizzle;
+  alignas(64) unsigned char map[128];
+};
+
+}  // namespace cuxb
+
+struct cuxb_ctx {
+  int device;
+  int sm_count;
+  int cc_major, cc_minor;
+  // reductions: per-block partials (float / int32 share the storage) + arrival ticket
+  void *red_partials;        // kReduceMaxBlocks * 8 bytes
+  unsigned int *red_ticket;  // zero at rest
+  // scan: tile states (64-bit), dynamic tile counter, launch epoch
+  unsigned long long *scan_state;
+  unsigned int *scan_counter;  // [0] tile ticket, [1] finished tiles
+  long long scan_state_tiles;
+  unsigned int scan_epoch;
+  // host-API staging
+  void *stage[4];
+  size_t stage_bytes[4];
+  cudaStream_t stage_stream;
+  // TMA descriptor cache
+  cuxb::TmaCacheEntry tma_cache[16];
+  int tma_cache_n;
+  int tma_cache_next;
+  std::mutex *mu;
+};
+
+namespace cuxb {
+int ensure_device(cuxb_ctx *ctx);
+int stage_reserve(cuxb_ctx *ctx, int slot, size_t bytes, void **out);
+}  // namespace cuxb

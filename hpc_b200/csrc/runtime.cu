@@ -1,0 +1,209 @@
+// runtime.cu -- context, memory, stream/event entry points of the cuxb C ABI.
+// These replace the CUDA-runtime calls cux makes from Array4D, GpuTimer and
+// OpAssistor (0-frameworks/cux/include/array.h:84-114, util/timer.h:16-38,
+// operator/op_assistor.h:100-143) so that host code needs no CUDA header.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace cuxb {
+
+static thread_local char t_err[512] = "no error";
+std::atomic<long long> g_launches{0};
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(t_err, sizeof(t_err), fmt, ap);
+  va_end(ap);
+}
+
+int ensure_device(cuxb_ctx *ctx) {
+  CUXB_REQUIRE(ctx != nullptr, CUXB_ERR_INVALID, "null cuxb_ctx");
+  int cur = -1;
+  CUXB_CUDA(cudaGetDevice(&cur));
+  if (cur != ctx->device) CUXB_CUDA(cudaSetDevice(ctx->device));
+  return 0;
+}
+
+int stage_reserve(cuxb_ctx *ctx, int slot, size_t bytes, void **out) {
+  if (ctx->stage_bytes[slot] < bytes) {
+    if (ctx->stage[slot]) CUXB_CUDA(cudaFree(ctx->stage[slot]));
+    ctx->stage[slot] = nullptr;
+    ctx->stage_bytes[slot] = 0;
+    CUXB_CUDA(cudaMalloc(&ctx->stage[slot], bytes));
+    ctx->stage_bytes[slot] = bytes;
+  }
+  *out = ctx->stage[slot];
+  return 0;
+}
+
+}  // namespace cuxb
+
+using namespace cuxb;
+
+CUXB_API const char *cuxb_last_error_string(void) { return t_err; }
+CUXB_API const char *cuxb_version(void) { return "cuxb 0.1 (sm_100a)"; }
+CUXB_API long long cuxb_launch_count(void) { return g_launches.load(); }
+
+CUXB_API int cuxb_ctx_create(int device, cuxb_ctx **out) {
+  CUXB_REQUIRE(out != nullptr, CUXB_ERR_INVALID, "cuxb_ctx_create: out is null");
+  *out = nullptr;
+  int count = 0;
+  CUXB_CUDA(cudaGetDeviceCount(&count));
+  CUXB_REQUIRE(device >= 0 && device < count, CUXB_ERR_INVALID,
+               "cuxb_ctx_create: device %d out of range (%d devices)", device, count);
+  CUXB_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUXB_CUDA(cudaGetDeviceProperties(&prop, device));
+  // No fallback path exists: the kernels are sm_100a-only (tcgen05/TMEM/TMA).
+  CUXB_REQUIRE(prop.major == 10, CUXB_ERR_UNSUPPORTED,
+               "cuxb needs a Blackwell sm_100 device, found sm_%d%d (%s)", prop.major, prop.minor,
+               prop.name);
+  cuxb_ctx *c = new cuxb_ctx();
+  memset(c, 0, sizeof(*c));
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  c->cc_major = prop.major;
+  c->cc_minor = prop.minor;
+  c->mu = new std::mutex();
+  cudaError_t e;
+  e = cudaMalloc(&c->red_partials, kReduceMaxBlocks * 8);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&c->red_ticket, 256);
+  if (e == cudaSuccess) e = cudaMemset(c->red_ticket, 0, 256);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&c->scan_counter, 256);
+  if (e == cudaSuccess) e = cudaMemset(c->scan_counter, 0, 256);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stage_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    set_error("cuxb_ctx_create: %s", cudaGetErrorString(e));
+    cuxb_ctx_destroy(c);
+    return (int)e;
+  }
+  c->scan_epoch = 0;
+  *out = c;
+  return 0;
+}
+
+CUXB_API int cuxb_ctx_destroy(cuxb_ctx *c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  if (c->red_partials) cudaFree(c->red_partials);
+  if (c->red_ticket) cudaFree(c->red_ticket);
+  if (c->scan_state) cudaFree(c->scan_state);
+  if (c->scan_counter) cudaFree(c->scan_counter);
+  for (int i = 0; i < 4; i++)
+    if (c->stage[i]) cudaFree(c->stage[i]);
+  if (c->stage_stream) cudaStreamDestroy(c->stage_stream);
+  delete c->mu;
+  delete c;
+  return 0;
+}
+
+CUXB_API int cuxb_ctx_device(const cuxb_ctx *c) { return c ? c->device : -1; }
+CUXB_API int cuxb_ctx_sm_count(const cuxb_ctx *c) { return c ? c->sm_count : 0; }
+
+CUXB_API int cuxb_malloc(void **p, size_t bytes) {
+  CUXB_REQUIRE(p != nullptr, CUXB_ERR_INVALID, "cuxb_malloc: null out pointer");
+  CUXB_CUDA(cudaMalloc(p, bytes ? bytes : 1));
+  return 0;
+}
+CUXB_API int cuxb_free(void *p) {
+  if (p) CUXB_CUDA(cudaFree(p));
+  return 0;
+}
+CUXB_API int cuxb_malloc_host(void **p, size_t bytes) {
+  CUXB_REQUIRE(p != nullptr, CUXB_ERR_INVALID, "cuxb_malloc_host: null out pointer");
+  CUXB_CUDA(cudaMallocHost(p, bytes ? bytes : 1));
+  return 0;
+}
+CUXB_API int cuxb_free_host(void *p) {
+  if (p) CUXB_CUDA(cudaFreeHost(p));
+  return 0;
+}
+static int copy(void *dst, const void *src, size_t bytes, void *stream, cudaMemcpyKind kind) {
+  if (bytes == 0) return 0;
+  CUXB_REQUIRE(dst && src, CUXB_ERR_INVALID, "cuxb_memcpy: null pointer");
+  // cux semantics are synchronous cudaMemcpy (array.h:95,110); with an explicit
+  // stream the copy is asynchronous on that stream.
+  if (stream)
+    CUXB_CUDA(cudaMemcpyAsync(dst, src, bytes, kind, (cudaStream_t)stream));
+  else
+    CUXB_CUDA(cudaMemcpy(dst, src, bytes, kind));
+  return 0;
+}
+CUXB_API int cuxb_memcpy_h2d(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyHostToDevice); }
+CUXB_API int cuxb_memcpy_d2h(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyDeviceToHost); }
+CUXB_API int cuxb_memcpy_d2d(void *d, const void *s, size_t n, void *st) { return copy(d, s, n, st, cudaMemcpyDeviceToDevice); }
+CUXB_API int cuxb_memset(void *d, int v, size_t n, void *st) {
+  if (n == 0) return 0;
+  CUXB_REQUIRE(d, CUXB_ERR_INVALID, "cuxb_memset: null pointer");
+  if (st)
+    CUXB_CUDA(cudaMemsetAsync(d, v, n, (cudaStream_t)st));
+  else
+    CUXB_CUDA(cudaMemset(d, v, n));
+  return 0;
+}
+CUXB_API int cuxb_set_device(int device) {
+  CUXB_CUDA(cudaSetDevice(device));
+  return 0;
+}
+CUXB_API int cuxb_device_count(int *count) {
+  CUXB_REQUIRE(count, CUXB_ERR_INVALID, "null");
+  CUXB_CUDA(cudaGetDeviceCount(count));
+  return 0;
+}
+CUXB_API int cuxb_device_sync(void) {
+  CUXB_CUDA(cudaDeviceSynchronize());
+  return 0;
+}
+CUXB_API int cuxb_device_name(int device, char *buf, size_t buflen) {
+  CUXB_REQUIRE(buf && buflen, CUXB_ERR_INVALID, "null");
+  cudaDeviceProp prop;
+  CUXB_CUDA(cudaGetDeviceProperties(&prop, device));
+  snprintf(buf, buflen, "%s", prop.name);
+  return 0;
+}
+
+CUXB_API int cuxb_stream_create(void **s) {
+  CUXB_REQUIRE(s, CUXB_ERR_INVALID, "null");
+  cudaStream_t st;
+  CUXB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  *s = st;
+  return 0;
+}
+CUXB_API int cuxb_stream_destroy(void *s) {
+  if (s) CUXB_CUDA(cudaStreamDestroy((cudaStream_t)s));
+  return 0;
+}
+CUXB_API int cuxb_stream_sync(void *s) {
+  CUXB_CUDA(cudaStreamSynchronize((cudaStream_t)s));
+  return 0;
+}
+CUXB_API int cuxb_event_create(void **e) {
+  CUXB_REQUIRE(e, CUXB_ERR_INVALID, "null");
+  cudaEvent_t ev;
+  CUXB_CUDA(cudaEventCreate(&ev));
+  *e = ev;
+  return 0;
+}
+CUXB_API int cuxb_event_destroy(void *e) {
+  if (e) CUXB_CUDA(cudaEventDestroy((cudaEvent_t)e));
+  return 0;
+}
+CUXB_API int cuxb_event_record(void *e, void *s) {
+  CUXB_CUDA(cudaEventRecord((cudaEvent_t)e, (cudaStream_t)s));
+  return 0;
+}
+CUXB_API int cuxb_event_sync(void *e) {
+  CUXB_CUDA(cudaEventSynchronize((cudaEvent_t)e));
+  return 0;
+}
+CUXB_API int cuxb_event_elapsed_ms(void *a, void *b, float *ms) {
+  CUXB_REQUIRE(ms, CUXB_ERR_INVALID, "null");
+  CUXB_CUDA(cudaEventSynchronize((cudaEvent_t)b));
+  CUXB_CUDA(cudaEventElapsedTime(ms, (cudaEvent_t)a, (cudaEvent_t)b));
+  return 0;
+}

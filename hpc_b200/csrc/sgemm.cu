@@ -1,0 +1,218 @@
+// sgemm.cu -- fp32 GEMM on CUDA cores (FFMA), C = alpha*A*B + beta*C, row-major.
+//
+// Replaces GemmDeviceV0/V1/V2 + cublasSgemm (0-frameworks/cux/src/operator/
+// gemm.cu:17-130,237-238) and the GemmKernelv1..v5 study (cuda/gemm_fp32.cu:
+// 102-528).  The reference's best kernel is a 32x32 CTA tile with a 4x4 register
+// micro-tile and no software pipelining; this one is built for the B200 SM:
+//
+//   CTA tile 128x128x16, 256 threads (8 warps as 2x4), 8x8 register micro-tile
+//   per thread split 4+4 in both directions so that every shared-memory read is
+//   a conflict-free LDS.128 whose 32 lanes touch only 128 (A) / 64 (B) distinct
+//   bytes -- 4 LDS.128 feed 64 FFMA.
+//   A is stored k-major (transposed) in shared memory, B as it lies.
+//   Global->shared goes through registers (LDG.128 for tile t+1 is issued before
+//   the FFMA block of tile t and stored after it), two shared-memory stages, one
+//   __syncthreads per k-tile.  Register fragments are double-buffered inside the
+//   tile.  CTAs are rasterised in groups of 8 tile-rows so that the B panel a
+//   wave needs stays in the 126 MB L2.
+//   2 CTAs per SM (<=128 registers, 33 KB shared each).
+//
+// Numerics: acc = fma(a, b, acc) over k in increasing order, then
+// C = alpha*acc + beta*C0 (beta == 0: C0 is not read).  With the reference's
+// integer-valued fills every partial sum is exact, so the result is bit-identical
+// to GemmHostV0 (gemm.cpp:13-34); for general floats see tests/ for the tolerance.
+#include "common.cuh"
+
+namespace cuxb {
+
+constexpr int SG_BM = 128, SG_BN = 128, SG_BK = 16;
+constexpr int SG_THREADS = 256;
+constexpr int SG_LDA = SG_BM + 4;  // padded k-major A rows
+constexpr int SG_GROUP_M = 8;
+
+struct SgemmArgs {
+  int M, N, K;
+  float alpha, beta;
+  const float *A;
+  int lda;
+  const float *B;
+  int ldb;
+  float *C;
+  int ldc;
+  int tiles_m, tiles_n;
+};
+
+template <bool FAST>
+__global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p) {
+  __shared__ __align__(16) float As[2][SG_BK][SG_LDA];
+  __shared__ __align__(16) float Bs[2][SG_BK][SG_BN];
+
+  const int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int warp_m = warp >> 2, warp_n = warp & 3;   // 2 x 4 warps
+  const int lane_m = lane >> 2, lane_n = lane & 3;   // 8 x 4 lanes
+  // rows owned: tm0 + {0..3} and tm0 + 32 + {0..3};  cols: tn0 + {0..3} and tn0 + 16 + {0..3}
+  const int tm0 = warp_m * 64 + lane_m * 4;
+  const int tn0 = warp_n * 32 + lane_n * 4;
+
+  // grouped rasterisation
+  const int pid = blockIdx.x;
+  const int per_group = SG_GROUP_M * p.tiles_n;
+  const int group = pid / per_group;
+  const int first_m = group * SG_GROUP_M;
+  const int gsz = min(p.tiles_m - first_m, SG_GROUP_M);
+  const int tile_m = first_m + (pid % per_group) % gsz;
+  const int tile_n = (pid % per_group) / gsz;
+  const int m_base = tile_m * SG_BM, n_base = tile_n * SG_BN;
+
+  // global->shared assignment
+  const int a_row = tid >> 2, a_k4 = (tid & 3) * 4;  // + 64*i rows
+  const int b_k = tid >> 5, b_n4 = (tid & 31) * 4;   // + 8*i k-rows
+
+  float4 ra[2], rb[2];
+  auto gload = [&](int k0) {
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const int m = m_base + a_row + 64 * i;
+      const int k = k0 + a_k4;
+      if (FAST) {
+        ra[i] = __ldg(reinterpret_cast<const float4 *>(p.A + (size_t)m * p.lda + k));
+      } else {
+        float t[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) t[c] = (m < p.M && k + c < p.K) ? p.A[(size_t)m * p.lda + k + c] : 0.f;
+        ra[i] = make_float4(t[0], t[1], t[2], t[3]);
+      }
+      const int kb = k0 + b_k + 8 * i;
+      const int n = n_base + b_n4;
+      if (FAST) {
+        rb[i] = __ldg(reinterpret_cast<const float4 *>(p.B + (size_t)kb * p.ldb + n));
+      } else {
+        float t[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) t[c] = (kb < p.K && n + c < p.N) ? p.B[(size_t)kb * p.ldb + n + c] : 0.f;
+        rb[i] = make_float4(t[0], t[1], t[2], t[3]);
+      }
+    }
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const int m = a_row + 64 * i;
+      As[buf][a_k4 + 0][m] = ra[i].x;
+      As[buf][a_k4 + 1][m] = ra[i].y;
+      As[buf][a_k4 + 2][m] = ra[i].z;
+      As[buf][a_k4 + 3][m] = ra[i].w;
+      *reinterpret_cast<float4 *>(&Bs[buf][b_k + 8 * i][b_n4]) = rb[i];
+    }
+  };
+
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+
+  const int KT = (p.K + SG_BK - 1) / SG_BK;
+  gload(0);
+  sstore(0);
+  __syncthreads();
+
+  float af[2][8], bf[2][8];
+  auto lfrag = [&](int buf, int k, int s) {
+    const float4 a0 = *reinterpret_cast<const float4 *>(&As[buf][k][tm0]);
+    const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][k][tm0 + 32]);
+    const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[buf][k][tn0]);
+    const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[buf][k][tn0 + 16]);
+    af[s][0] = a0.x, af[s][1] = a0.y, af[s][2] = a0.z, af[s][3] = a0.w;
+    af[s][4] = a1.x, af[s][5] = a1.y, af[s][6] = a1.z, af[s][7] = a1.w;
+    bf[s][0] = b0.x, bf[s][1] = b0.y, bf[s][2] = b0.z, bf[s][3] = b0.w;
+    bf[s][4] = b1.x, bf[s][5] = b1.y, bf[s][6] = b1.z, bf[s][7] = b1.w;
+  };
+
+  for (int kt = 0; kt < KT; kt++) {
+    const int buf = kt & 1;
+    const bool more = kt + 1 < KT;
+    if (more) gload((kt + 1) * SG_BK);
+    lfrag(buf, 0, 0);
+#pragma unroll
+    for (int k = 0; k < SG_BK; k++) {
+      if (k + 1 < SG_BK) lfrag(buf, k + 1, (k + 1) & 1);
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[i][j] = fmaf(af[k & 1][i], bf[k & 1][j], acc[i][j]);
+    }
+    if (more) sstore(buf ^ 1);
+    __syncthreads();
+  }
+
+  // epilogue
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const int m = m_base + tm0 + (i & 3) + (i >> 2) * 32;
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int n = n_base + tn0 + h * 16;
+      float *cp = p.C + (size_t)m * p.ldc + n;
+      if (FAST) {
+        float4 o;
+        if (p.beta != 0.f) {
+          const float4 c0 = *reinterpret_cast<const float4 *>(cp);
+          o.x = p.alpha * acc[i][h * 4 + 0] + p.beta * c0.x;
+          o.y = p.alpha * acc[i][h * 4 + 1] + p.beta * c0.y;
+          o.z = p.alpha * acc[i][h * 4 + 2] + p.beta * c0.z;
+          o.w = p.alpha * acc[i][h * 4 + 3] + p.beta * c0.w;
+        } else {
+          o.x = p.alpha * acc[i][h * 4 + 0];
+          o.y = p.alpha * acc[i][h * 4 + 1];
+          o.z = p.alpha * acc[i][h * 4 + 2];
+          o.w = p.alpha * acc[i][h * 4 + 3];
+        }
+        *reinterpret_cast<float4 *>(cp) = o;
+      } else if (m < p.M) {
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+          if (n + c < p.N) {
+            float o = p.alpha * acc[i][h * 4 + c];
+            if (p.beta != 0.f) o += p.beta * cp[c];
+            cp[c] = o;
+          }
+      }
+    }
+  }
+}
+
+const void *sgemm_kernel_symbol() { return (const void *)sgemm_kernel<true>; }
+
+}  // namespace cuxb
+
+using namespace cuxb;
+
+CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha,
+                            const float *A, int lda, const float *B, int ldb, float beta, float *C,
+                            int ldc) {
+  int rc = ensure_device(ctx);
+  if (rc) return rc;
+  CUXB_REQUIRE(M >= 0 && N >= 0 && K >= 0, CUXB_ERR_INVALID, "cuxb_sgemm_f32: negative dimension");
+  if (M == 0 || N == 0) return 0;
+  CUXB_REQUIRE(A && B && C, CUXB_ERR_INVALID, "cuxb_sgemm_f32: null pointer");
+  CUXB_REQUIRE(lda >= K && ldb >= N && ldc >= N, CUXB_ERR_INVALID,
+               "cuxb_sgemm_f32: leading dimension smaller than the row length");
+  SgemmArgs p;
+  p.M = M, p.N = N, p.K = K, p.alpha = alpha, p.beta = beta;
+  p.A = A, p.lda = lda, p.B = B, p.ldb = ldb, p.C = C, p.ldc = ldc;
+  p.tiles_m = (M + SG_BM - 1) / SG_BM;
+  p.tiles_n = (N + SG_BN - 1) / SG_BN;
+  const bool fast = (M % SG_BM == 0) && (N % SG_BN == 0) && (K % SG_BK == 0) && K > 0 &&
+                    (lda % 4 == 0) && (ldb % 4 == 0) && (ldc % 4 == 0) &&
+                    ((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0);
+  const unsigned int grid = (unsigned int)(p.tiles_m * p.tiles_n);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (fast)
+    sgemm_kernel<true><<<grid, SG_THREADS, 0, st>>>(p);
+  else
+    sgemm_kernel<false><<<grid, SG_THREADS, 0, st>>>(p);
+  CUXB_LAUNCHED();
+  return 0;
+}

@@ -1,0 +1,615 @@
+// umma_gemm.cu -- tensor-core GEMM for sm_100a: TMA -> shared memory -> tcgen05.mma
+// (accumulators in TMEM) -> tcgen05.ld epilogue.  One kernel template serves
+//
+//   cuxb_hgemm_f16_f32acc   fp16  A[M,K] x B[K,N]    (cux "gemm", FLOAT16 kernels:
+//                           0-frameworks/cux/src/operator/gemm.cu:266-269 cublasSgemmEx;
+//                           cuda/gemm_fp16_wmma.cu:123-700 wmma study, fp32 accumulate
+//                           as its CPU oracle GemmHostV1 :75-90 does)
+//   cuxb_linear_f16/bf16    16-bit A[M,K] x Bt[N,K]^T (simd/x86/linear.cpp:137-196)
+//   cuxb_linear_s8_s32      int8  A[M,K] x Bt[N,K]^T -> int32 (linear.cpp:199-237)
+//
+// Design (see DESIGN.md "tensor-core GEMM"):
+//   * persistent grid, one CTA per SM; CTAs are paired into 2-CTA clusters and the
+//     pair issues ONE tcgen05.mma.cta_group::2 of 256 x 256 x 16 per step: each CTA
+//     holds 128 rows of A and 128 columns of B, so neither operand is loaded twice
+//     inside the pair.  (kCtaGroup = 1 is the single-CTA 128 x 256 variant.)
+//   * warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane, leader CTA only),
+//     warp 2 = TMEM allocator, warps 4..7 = epilogue (one TMEM lane quarter each).
+//   * kStages-deep shared-memory ring (128B-swizzled tiles, 64 k-elements = 128 bytes
+//     per row) guarded by full/empty mbarriers; the full barrier lives in the leader
+//     CTA and receives the byte counts of BOTH CTAs' TMA loads.
+//   * two 256-column fp32/int32 accumulators in TMEM (all 512 columns): the epilogue of
+//     tile t (tcgen05.ld -> alpha/beta -> convert -> 16-byte global stores) overlaps the
+//     mainloop of tile t+1.
+//   * B given as [K,N] (cux layout) is consumed as an "MN-major" UMMA operand: TMA boxes
+//     of 64 n x 64 k land as 128-byte rows and the descriptor walks them with
+//     LBO = 8 KiB (next 64 columns) / SBO = 1 KiB (next 8 k-rows); no transpose pass.
+//   * ragged M/N/K: TMA zero-fills out-of-bounds reads, stores are guarded.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace cuxb {
+
+enum { KIND_F16 = 0, KIND_BF16 = 1, KIND_S8 = 2 };
+
+constexpr int UG_BLOCK_M = 128;   // rows of A per CTA
+constexpr int UG_BLOCK_N = 256;   // columns per MMA (per CTA pair / per CTA when kCtaGroup==1)
+constexpr int UG_ROW_BYTES = 128; // bytes of K per shared-memory row (one swizzle span)
+constexpr int UG_THREADS = 256;
+constexpr int UG_GROUP_M = 8;
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// arrive on the barrier at this offset in the even (leader) CTA of the pair
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_local(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok != 0;
+}
+// Bounded wait: a pipeline bug must end in a trap (reported as a launch failure), never a hang.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin)
+    if (spin > 40000000u) __trap();
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+template <int CG>
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
+  if (CG == 1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+  } else {
+    // both CTAs of the pair run this; completion bytes are counted on the leader's barrier
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1) : "memory");
+  }
+}
+template <int CG>
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+  if (CG == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  } else {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+}
+template <int CG>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  if (CG == 1)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+  else
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+template <int CG, int KIND>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if (KIND == KIND_S8) {
+    if (CG == 1)
+      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else
+      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+  } else {
+    if (CG == 1)
+      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    else
+      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+// tcgen05.commit: the barrier is arrived on when every MMA issued so far by this thread has
+// completed.  With CG==2 the arrival is multicast to the same barrier offset in both CTAs.
+template <int CG>
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  if (CG == 1)
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+  else
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor (sm_100 format): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46),
+// version=1 [46,48), layout type [61,64) with 2 = 128-byte swizzle.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= 1ull << 46;
+  d |= 2ull << 61;
+  return d;
+}
+
+// Instruction descriptor: c_format [4,6) (1=f32, 2=s32), a_format [7,10), b_format [10,13)
+// (f16=0, bf16=1; signed int8=1), a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 [17,23),
+// M>>4 [24,29).
+template <int KIND, bool B_MN>
+__host__ __device__ constexpr uint32_t make_idesc(int mma_m, int mma_n) {
+  uint32_t d = 0;
+  const uint32_t fmt = (KIND == KIND_F16) ? 0u : 1u;  // bf16 = 1, signed int8 = 1
+  d |= ((KIND == KIND_S8) ? 2u : 1u) << 4;
+  d |= fmt << 7;
+  d |= fmt << 10;
+  d |= (B_MN ? 1u : 0u) << 16;
+  d |= (uint32_t)(mma_n >> 3) << 17;
+  d |= (uint32_t)(mma_m >> 4) << 24;
+  return d;
+}
+
+struct UmmaArgs {
+  int M, N, K;         // problem
+  int ldc;             // elements
+  void *C;
+  float alpha, beta;
+  int tiles_m, tiles_n;  // in units of (UG_BLOCK_M * kCtaGroup) x UG_BLOCK_N
+  int k_blocks;
+};
+
+template <int CG>
+struct UmmaCfg {
+  static constexpr int kBRows = UG_BLOCK_N / CG;                    // rows (K-major) / columns (MN-major) of B per CTA
+  static constexpr int kABytes = UG_BLOCK_M * UG_ROW_BYTES;         // 16 KiB
+  static constexpr int kBBytes = kBRows * UG_ROW_BYTES;             // 16 / 32 KiB
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (CG == 2) ? 6 : 4;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+// out-type helpers ---------------------------------------------------------------------------
+template <int CT> struct OutT;
+template <> struct OutT<CUXB_FLOAT16> { typedef __half type; };
+template <> struct OutT<CUXB_BFLOAT16> { typedef __nv_bfloat16 type; };
+template <> struct OutT<CUXB_FLOAT32> { typedef float type; };
+template <> struct OutT<CUXB_INT32> { typedef int32_t type; };
+
+__device__ __forceinline__ float out_to_f32(__half v) { return __half2float(v); }
+__device__ __forceinline__ float out_to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float out_to_f32(float v) { return v; }
+__device__ __forceinline__ void f32_to_out(float f, __half &o) { o = __float2half_rn(f); }
+__device__ __forceinline__ void f32_to_out(float f, __nv_bfloat16 &o) { o = __float2bfloat16_rn(f); }
+__device__ __forceinline__ void f32_to_out(float f, float &o) { o = f; }
+
+// 8 consecutive outputs of one row: v[0..7] are raw accumulator words
+template <int KIND, typename OT>
+__device__ __forceinline__ void store8(OT *cp, const uint32_t *v, float alpha, float beta, bool full_cols,
+                                       int cols_left) {
+  if constexpr (KIND == KIND_S8) {
+    int32_t *ip = reinterpret_cast<int32_t *>(cp);
+    if (full_cols) {
+      *reinterpret_cast<uint4 *>(ip) = make_uint4(v[0], v[1], v[2], v[3]);
+      *reinterpret_cast<uint4 *>(ip + 4) = make_uint4(v[4], v[5], v[6], v[7]);
+    } else {
+      for (int c = 0; c < 8 && c < cols_left; c++) ip[c] = (int32_t)v[c];
+    }
+  } else {
+  OT o[8];
+  if (beta != 0.f) {
+    OT c0[8];
+    if (full_cols) {
+      if (sizeof(OT) == 2) {
+        *reinterpret_cast<uint4 *>(c0) = *reinterpret_cast<const uint4 *>(cp);
+      } else {
+        *reinterpret_cast<uint4 *>(c0) = *reinterpret_cast<const uint4 *>(cp);
+        *reinterpret_cast<uint4 *>(c0 + 4) = *reinterpret_cast<const uint4 *>(cp + 4);
+      }
+    } else {
+      for (int c = 0; c < 8; c++) c0[c] = (c < cols_left) ? cp[c] : OT();
+    }
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+      // two separately rounded products and one add, as the CPU oracle does (no fma contraction)
+      const float t0 = __fmul_rn(alpha, __uint_as_float(v[c]));
+      const float t1 = __fmul_rn(beta, out_to_f32(c0[c]));
+      f32_to_out(__fadd_rn(t0, t1), o[c]);
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < 8; c++) f32_to_out(__fmul_rn(alpha, __uint_as_float(v[c])), o[c]);
+  }
+  if (full_cols) {
+    if (sizeof(OT) == 2) {
+      *reinterpret_cast<uint4 *>(cp) = *reinterpret_cast<const uint4 *>(o);
+    } else {
+      *reinterpret_cast<uint4 *>(cp) = *reinterpret_cast<const uint4 *>(o);
+      *reinterpret_cast<uint4 *>(cp + 4) = *reinterpret_cast<const uint4 *>(o + 4);
+    }
+  } else {
+    for (int c = 0; c < 8 && c < cols_left; c++) cp[c] = o[c];
+  }
+  }
+}
+
+// --------------------------------------------------------------------------------- the kernel
+template <int KIND, bool B_MN, int CT, int CG>
+__global__ void __launch_bounds__(UG_THREADS, 1)
+umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                 const UmmaArgs p) {
+  typedef UmmaCfg<CG> Cfg;
+  typedef typename OutT<CT>::type OT;
+  constexpr int kStages = Cfg::kStages;
+  constexpr int kElemBytes = (KIND == KIND_S8) ? 1 : 2;
+  constexpr int kBlockK = UG_ROW_BYTES / kElemBytes;  // 64 or 128 elements
+  constexpr int kMmaK = 32 / kElemBytes;              // 16 or 32 elements = 32 bytes
+  constexpr int kMmaPerStage = kBlockK / kMmaK;       // 4
+  constexpr uint32_t kIdesc = make_idesc<KIND, B_MN>(UG_BLOCK_M * CG, UG_BLOCK_N);
+  constexpr uint32_t kTmemCols = 512;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + kStages * Cfg::kStageBytes;
+  // barrier layout (8 bytes each): full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem ptr
+  const uint32_t full_bar = bar_base, empty_bar = bar_base + 8 * kStages;
+  const uint32_t tfull_bar = bar_base + 16 * kStages, tempty_bar = tfull_bar + 16;
+  const uint32_t tmem_slot = tempty_bar + 16;
+  uint8_t *smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_gen + (tmem_slot - smem_base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
+  const bool is_leader = cta_rank == 0;
+
+  if (warp == 0 && elect_one()) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+  }
+  if (warp == 1 && elect_one()) {
+    for (int s = 0; s < kStages; s++) {
+      mbar_init(full_bar + 8 * s, 1);
+      mbar_init(empty_bar + 8 * s, 1);
+    }
+    for (int a = 0; a < 2; a++) {
+      mbar_init(tfull_bar + 8 * a, 1);
+      mbar_init(tempty_bar + 8 * a, 4 * CG);  // one arrival per epilogue warp of every CTA in the pair
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<CG>(tmem_slot, kTmemCols);
+  tc_fence_before();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  const int num_clusters = gridDim.x / CG;
+  const int cluster_id = blockIdx.x / CG;
+  const int total_tiles = p.tiles_m * p.tiles_n;
+  const int per_group = UG_GROUP_M * p.tiles_n;
+
+  auto tile_coord = [&](int t, int &tm, int &tn) {
+    const int group = t / per_group;
+    const int first_m = group * UG_GROUP_M;
+    const int gsz = min(p.tiles_m - first_m, UG_GROUP_M);
+    tm = first_m + (t % per_group) % gsz;
+    tn = (t % per_group) / gsz;
+  };
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs of a pair; one elected lane) =====================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+        int tm, tn;
+        tile_coord(t, tm, tn);
+        const int m0 = (tm * CG + (int)cta_rank) * UG_BLOCK_M;
+        const int n0 = tn * UG_BLOCK_N + (int)cta_rank * Cfg::kBRows;
+        for (int kb = 0; kb < p.k_blocks; kb++) {
+          mbar_wait(empty_bar + 8 * stage, phase ^ 1);
+          const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
+          const uint32_t sb = sa + Cfg::kABytes;
+          const uint32_t fb = full_bar + 8 * stage;
+          if (is_leader) mbar_expect_tx(fb, Cfg::kStageBytes * CG);
+          const int k0 = kb * kBlockK;
+          tma_load_2d<CG>(sa, &map_a, fb, k0, m0);
+          if (B_MN) {
+            // B[K,N]: boxes of 64 n x kBlockK k, one per 64 columns
+#pragma unroll
+            for (int c = 0; c < Cfg::kBRows / 64; c++)
+              tma_load_2d<CG>(sb + c * (kBlockK * UG_ROW_BYTES), &map_b, fb, n0 + c * 64, k0);
+          } else {
+            tma_load_2d<CG>(sb, &map_b, fb, k0, n0);
+          }
+          if (++stage == kStages) stage = 0, phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA, one elected lane) =====================
+    if (is_leader && elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+        mbar_wait(tempty_bar + 8 * acc, acc_phase ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * UG_BLOCK_N;
+        for (int kb = 0; kb < p.k_blocks; kb++) {
+          mbar_wait(full_bar + 8 * stage, phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
+          const uint32_t sb = sa + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < kMmaPerStage; k++) {
+            // K-major: 32 bytes further along the 128-byte swizzled row;
+            // MN-major: kMmaK k-rows of 128 bytes further down.
+            const uint64_t adesc = make_smem_desc(sa + k * 32, 16, 1024);
+            const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (kMmaK * UG_ROW_BYTES), kBlockK * UG_ROW_BYTES, 1024)
+                                        : make_smem_desc(sb + k * 32, 16, 1024);
+            umma<CG, KIND>(tmem_d, adesc, bdesc, kIdesc, (kb | k) != 0);
+          }
+          umma_commit<CG>(empty_bar + 8 * stage);  // frees the smem slot (in both CTAs) when the MMAs retire
+          if (++stage == kStages) stage = 0, phase ^= 1;
+        }
+        umma_commit<CG>(tfull_bar + 8 * acc);      // accumulator complete -> epilogue (both CTAs)
+        if (++acc == 2) acc = 0, acc_phase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== epilogue: TMEM -> registers -> global =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    OT *C = reinterpret_cast<OT *>(p.C);
+    for (int t = cluster_id; t < total_tiles; t += num_clusters) {
+      int tm, tn;
+      tile_coord(t, tm, tn);
+      const int row = (tm * CG + (int)cta_rank) * UG_BLOCK_M + q * 32 + lane;
+      const int n0 = tn * UG_BLOCK_N;
+      mbar_wait(tfull_bar + 8 * acc, acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * UG_BLOCK_N;
+#pragma unroll 1
+      for (int cb = 0; cb < UG_BLOCK_N / 32; cb++) {
+        uint32_t v[32];
+        tmem_ld32(taddr + cb * 32, v);
+        tmem_ld_wait();
+        if (cb == UG_BLOCK_N / 32 - 1) {
+          // every word of this accumulator is now in registers: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (CG == 2) mbar_arrive_leader(tempty_bar + 8 * acc);
+            else mbar_arrive_local(tempty_bar + 8 * acc);
+          }
+        }
+        const int col = n0 + cb * 32;
+        if (row < p.M && col < p.N) {
+          OT *cp = C + (size_t)row * p.ldc + col;
+#pragma unroll
+          for (int g = 0; g < 4; g++) {
+            const int left = p.N - (col + g * 8);
+            if (left > 0) store8<KIND, OT>(cp + g * 8, v + g * 8, p.alpha, p.beta, left >= 8, left);
+          }
+        }
+      }
+      if (++acc == 2) acc = 0, acc_phase ^= 1;
+    }
+  }
+
+  // teardown
+  tc_fence_before();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 2) tmem_dealloc<CG>(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void *p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = (EncodeTiledFn)p;
+  return fn;
+}
+
+// 2-D row-major tensor [rows, cols] of `ebytes`-byte elements, row pitch ld elements;
+// box = box_cols x box_rows, 128-byte swizzle.
+static int make_map(CUtensorMap *map, const void *base, int ebytes, CUtensorMapDataType dt, uint64_t rows,
+                    uint64_t cols, uint64_t ld, uint32_t box_cols, uint32_t box_rows) {
+  EncodeTiledFn enc = get_encode();
+  CUXB_REQUIRE(enc != nullptr, CUXB_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * (uint64_t)ebytes};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUXB_REQUIRE(r == CUDA_SUCCESS, CUXB_ERR_INVALID,
+               "cuTensorMapEncodeTiled failed (%d): base=%p rows=%llu cols=%llu ld=%llu box=%ux%u", (int)r, base,
+               (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_cols, box_rows);
+  return 0;
+}
+
+static int g_force_cta_group = 0;  // test hook: 0 = auto (2), 1 or 2
+
+template <int KIND, bool B_MN, int CT, int CG>
+static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, float alpha, const void *A, int lda,
+                       const void *B, int ldb, float beta, void *C, int ldc) {
+  typedef UmmaCfg<CG> Cfg;
+  constexpr int ebytes = (KIND == KIND_S8) ? 1 : 2;
+  constexpr int kBlockK = UG_ROW_BYTES / ebytes;
+  const CUtensorMapDataType dt = (KIND == KIND_S8)    ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                 : (KIND == KIND_F16) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                      : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUtensorMap ma, mb;
+  int rc = make_map(&ma, A, ebytes, dt, (uint64_t)M, (uint64_t)K, (uint64_t)lda, kBlockK, UG_BLOCK_M);
+  if (rc) return rc;
+  if (B_MN)
+    rc = make_map(&mb, B, ebytes, dt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, kBlockK);
+  else
+    rc = make_map(&mb, B, ebytes, dt, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, kBlockK, Cfg::kBRows);
+  if (rc) return rc;
+
+  UmmaArgs p;
+  p.M = M, p.N = N, p.K = K, p.ldc = ldc, p.C = C, p.alpha = alpha, p.beta = beta;
+  p.tiles_m = (int)div_up(M, UG_BLOCK_M * CG);
+  p.tiles_n = (int)div_up(N, UG_BLOCK_N);
+  p.k_blocks = (int)div_up(K, kBlockK);
+  const int total = p.tiles_m * p.tiles_n;
+  int clusters = ctx->sm_count / CG;
+  if (clusters > total) clusters = total;
+
+  auto kern = umma_gemm_kernel<KIND, B_MN, CT, CG>;
+  CUXB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(clusters * CG, 1, 1);
+  cfg.blockDim = dim3(UG_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CUXB_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  g_launches.fetch_add(1);
+  return 0;
+}
+
+template <int KIND, bool B_MN, int CT>
+static int dispatch_cg(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, float alpha, const void *A, int lda,
+                       const void *B, int ldb, float beta, void *C, int ldc) {
+  const int cg = g_force_cta_group ? g_force_cta_group : 2;
+  if (cg == 1) return launch_umma<KIND, B_MN, CT, 1>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+  return launch_umma<KIND, B_MN, CT, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+}
+
+static int check_common(const char *name, cuxb_ctx *ctx, int M, int N, int K, const void *A, const void *B,
+                        const void *C, int ebytes, int lda, int ldb, int ldc, int cbytes) {
+  int rc = ensure_device(ctx);
+  if (rc) return rc;
+  CUXB_REQUIRE(M >= 0 && N >= 0 && K >= 0, CUXB_ERR_INVALID, "%s: negative dimension", name);
+  if (M == 0 || N == 0) return -1;  // nothing to do
+  CUXB_REQUIRE(K > 0, CUXB_ERR_UNSUPPORTED, "%s: K must be positive", name);
+  CUXB_REQUIRE(A && B && C, CUXB_ERR_INVALID, "%s: null pointer", name);
+  CUXB_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && ((uintptr_t)C & 15) == 0,
+               CUXB_ERR_UNSUPPORTED, "%s: A, B and C must be 16-byte aligned (TMA / vector stores)", name);
+  CUXB_REQUIRE((lda * ebytes) % 16 == 0 && (ldb * ebytes) % 16 == 0 && (ldc * cbytes) % 16 == 0,
+               CUXB_ERR_UNSUPPORTED, "%s: row pitches must be multiples of 16 bytes (lda=%d ldb=%d ldc=%d)", name,
+               lda, ldb, ldc);
+  return 0;
+}
+
+const void *umma_kernel_symbol() { return (const void *)umma_gemm_kernel<KIND_F16, true, CUXB_FLOAT16, 2>; }
+int umma_smem_bytes() { return UmmaCfg<2>::kSmemBytes; }
+
+}  // namespace cuxb
+
+using namespace cuxb;
+
+// test hook (not in cuxb.h): force the single-CTA (1) or paired-CTA (2) MMA variant; 0 = default
+CUXB_API int cuxb_debug_set_cta_group(int cg) {
+  if (cg < 0 || cg > 2) return CUXB_ERR_INVALID;
+  g_force_cta_group = cg;
+  return 0;
+}
+
+CUXB_API int cuxb_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const void *A,
+                                   int lda, const void *B, int ldb, float beta, void *C, int ldc, int c_dtype) {
+  CUXB_REQUIRE(c_dtype == CUXB_FLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,
+               "cuxb_hgemm_f16_f32acc: c_dtype must be CUXB_FLOAT16 or CUXB_FLOAT32");
+  int rc = check_common("cuxb_hgemm_f16_f32acc", ctx, M, N, K, A, B, C, 2, lda, ldb, ldc,
+                        c_dtype == CUXB_FLOAT16 ? 2 : 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  CUXB_REQUIRE(lda >= K && ldb >= N && ldc >= N, CUXB_ERR_INVALID, "cuxb_hgemm_f16_f32acc: leading dimension too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c_dtype == CUXB_FLOAT16)
+    return dispatch_cg<KIND_F16, true, CUXB_FLOAT16>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+  return dispatch_cg<KIND_F16, true, CUXB_FLOAT32>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+}
+
+CUXB_API int cuxb_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A, const void *Bt,
+                                    void *C, int c_dtype) {
+  CUXB_REQUIRE(c_dtype == CUXB_FLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,
+               "cuxb_linear_f16_f32acc: c_dtype must be CUXB_FLOAT16 or CUXB_FLOAT32");
+  int rc = check_common("cuxb_linear_f16_f32acc", ctx, M, N, K, A, Bt, C, 2, K, K, N, c_dtype == CUXB_FLOAT16 ? 2 : 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c_dtype == CUXB_FLOAT16)
+    return dispatch_cg<KIND_F16, false, CUXB_FLOAT16>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N);
+  return dispatch_cg<KIND_F16, false, CUXB_FLOAT32>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N);
+}
+
+CUXB_API int cuxb_linear_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A,
+                                     const void *Bt, void *C, int c_dtype) {
+  CUXB_REQUIRE(c_dtype == CUXB_BFLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,
+               "cuxb_linear_bf16_f32acc: c_dtype must be CUXB_BFLOAT16 or CUXB_FLOAT32");
+  int rc = check_common("cuxb_linear_bf16_f32acc", ctx, M, N, K, A, Bt, C, 2, K, K, N, c_dtype == CUXB_BFLOAT16 ? 2 : 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c_dtype == CUXB_BFLOAT16)
+    return dispatch_cg<KIND_BF16, false, CUXB_BFLOAT16>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N);
+  return dispatch_cg<KIND_BF16, false, CUXB_FLOAT32>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N);
+}
+
+CUXB_API int cuxb_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, int K, const int8_t *A, const int8_t *Bt,
+                                int32_t *C) {
+  int rc = check_common("cuxb_linear_s8_s32", ctx, M, N, K, A, Bt, C, 1, K, K, N, 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  return dispatch_cg<KIND_S8, false, CUXB_INT32>(ctx, (cudaStream_t)stream, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N);
+}

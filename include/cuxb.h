@@ -1,0 +1,176 @@
+/*
+ * cuxb.h -- C ABI of libcuxb.so: B200 (sm_100a) kernels for the cux operator set.
+ *
+ * This is the drop-in boundary.  Everything above it (the cux-compatible C++
+ * host layer in hpc_b200/cux/, the Python ctypes mirror in hpc_b200/capi.py, or
+ * the reference's own plugins -- see INTEGRATION.md) reaches CUDA only through
+ * these functions: plain pointers and sizes, no CUDA, torch or C++ types.
+ *
+ * Conventions
+ *   - every function returns 0 on success, else a non-zero code (a cudaError_t
+ *     value, or one of CUXB_ERR_*); cuxb_last_error_string() describes the most
+ *     recent failure on the calling thread.  Nothing throws.  The reference's
+ *     behaviour for the same failures is log + exit/abort
+ *     (0-frameworks/cux/include/util/util.h:69-95); the C++ layer maps non-zero
+ *     codes onto that.
+ *   - device pointers are opaque `void*` / typed pointers to DEVICE memory
+ *     unless the name ends in `_host`.
+ *   - `stream` is a cudaStream_t passed as void*; NULL is the legacy default
+ *     stream, which is what cux's GpuTimer records on
+ *     (0-frameworks/cux/include/util/timer.h:26-27).
+ *   - matrices are row-major with explicit leading dimensions, as cux passes
+ *     them (0-frameworks/cux/src/operator/gemm.cpp:458-463: lda=K, ldb=N, ldc=N).
+ *   - kernels never fall back to the CPU.  A missing device, a non-sm_100
+ *     device or an unsupported shape is an error.
+ */
+#ifndef CUXB_H_
+#define CUXB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CUXB_ERR_INVALID 100001   /* bad argument (null pointer, negative size, misalignment) */
+#define CUXB_ERR_UNSUPPORTED 100002 /* shape / device not supported by the sm_100a kernels */
+#define CUXB_ERR_TOO_LARGE 100003 /* size beyond a documented maximum */
+
+/* Element type tags, numerically equal to cux::TypeFlag
+ * (0-frameworks/cux/include/util/util.h:22-28) plus BFLOAT16. */
+#define CUXB_FLOAT32 0
+#define CUXB_INT32 1
+#define CUXB_FLOAT16 2
+#define CUXB_INT8 3
+#define CUXB_BFLOAT16 4
+
+typedef struct cuxb_ctx cuxb_ctx;
+
+/* ---- context: per-device workspace (block partials, scan tile states, TMA
+ * descriptors, staging buffers).  Replaces what cux::OpAssistor owns
+ * (0-frameworks/cux/include/operator/op_assistor.h:100-143: device, cuBLAS handle). */
+int cuxb_ctx_create(int device, cuxb_ctx **out);
+int cuxb_ctx_destroy(cuxb_ctx *ctx);
+int cuxb_ctx_device(const cuxb_ctx *ctx);
+int cuxb_ctx_sm_count(const cuxb_ctx *ctx);
+const char *cuxb_last_error_string(void);
+const char *cuxb_version(void);
+/* Number of kernel launches this library has issued in this process (all contexts). */
+long long cuxb_launch_count(void);
+
+/* ---- memory, replacing the cudaMalloc/cudaMemcpy/cudaMemset/cudaFree calls inside
+ * cux::Array4D (0-frameworks/cux/include/array.h:84-114, src/array.cpp:29-44). */
+int cuxb_malloc(void **dptr, size_t bytes);
+int cuxb_free(void *dptr);
+int cuxb_malloc_host(void **hptr, size_t bytes); /* pinned */
+int cuxb_free_host(void *hptr);
+int cuxb_memcpy_h2d(void *dst, const void *src, size_t bytes, void *stream);
+int cuxb_memcpy_d2h(void *dst, const void *src, size_t bytes, void *stream);
+int cuxb_memcpy_d2d(void *dst, const void *src, size_t bytes, void *stream);
+int cuxb_memset(void *dst, int value, size_t bytes, void *stream);
+int cuxb_set_device(int device);
+int cuxb_device_count(int *count);
+int cuxb_device_sync(void);
+int cuxb_device_name(int device, char *buf, size_t buflen);
+
+/* ---- streams and events, replacing cux::GpuTimer
+ * (0-frameworks/cux/include/util/timer.h:16-38). */
+int cuxb_stream_create(void **stream);
+int cuxb_stream_destroy(void *stream);
+int cuxb_stream_sync(void *stream);
+int cuxb_event_create(void **event);
+int cuxb_event_destroy(void *event);
+int cuxb_event_record(void *event, void *stream);
+int cuxb_event_sync(void *event);
+int cuxb_event_elapsed_ms(void *start, void *stop, float *ms);
+
+/* ---- reductions (HBM-bound).  Results OVERWRITE *res (device pointer); the
+ * summation order is fixed, so results are run-to-run identical.
+ *
+ * cuxb_dot_f32 replaces the body of DotGpuKernelIF::func
+ *   (0-frameworks/cux/include/operator/kernel_interface.h:30-35; kernels
+ *   DotDeviceV0/V1/V2 + cublasSdot, src/operator/dot_product.cu:9-112,203-204).
+ * cuxb_sum_f32 replaces ReduceKernelFp32V1/V2 (cuda/reduce_fp32.cu:33-116).
+ * cuxb_nrm2_f32 replaces Nrm2GpuKernelIF::func (kernel_interface.h:43-48;
+ *   Nrm2DeviceV0 + Sqrt + cublasSnrm2, src/operator/nrm2.cu:7-23,58-59); n<=0 -> 0,
+ *   n==1 -> |x0| as Nrm2HostV0 does (src/operator/nrm2.cpp:8-9). */
+int cuxb_dot_f32(cuxb_ctx *ctx, void *stream, long long n, const float *a, const float *b, float *res);
+int cuxb_sum_f32(cuxb_ctx *ctx, void *stream, long long n, const float *x, float *res);
+int cuxb_nrm2_f32(cuxb_ctx *ctx, void *stream, long long n, const float *x, float *res);
+/* int32 sum with two's-complement wrap-around (phase 1 of the multi-GPU scan). */
+int cuxb_sum_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *x, int32_t *res);
+
+/* ---- inclusive prefix scan, out[i] = seed + in[0] + ... + in[i], int32 with
+ * wrap-around.  Replaces VectorScanNormal/SIMDv1/SIMDv2
+ * (simd/x86/vector_scan.cpp:21-79) in the int element type of
+ * tbb/base_parallel_scan.cpp:62-65.  in == out (in place) is allowed. */
+int cuxb_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *in, int32_t *out, int32_t seed);
+/* fp32 variant (same recurrence; the order of additions differs from the serial
+ * reference). */
+int cuxb_scan_f32(cuxb_ctx *ctx, void *stream, long long n, const float *in, float *out, float seed);
+
+/* ---- GEMM: C = alpha * A[M,K] * B[K,N] + beta * C, row-major.
+ *
+ * cuxb_sgemm_f32 replaces GemmGpuKernelIF::func for TypeFlag::FLOAT32
+ *   (kernel_interface.h:61-72; GemmDeviceV0/V1/V2 + cublasSgemm,
+ *   src/operator/gemm.cu:17-130,237-238; cuda/gemm_fp32.cu:102-528).  CUDA cores (FFMA).
+ * cuxb_hgemm_f16_f32acc replaces the FLOAT16 entry (cublasSgemmEx,
+ *   src/operator/gemm.cu:266-269) and cuda/gemm_fp16_wmma.cu:123-700: fp16 A,B,
+ *   fp32 accumulate on tcgen05/TMEM, alpha/beta in fp32.  c_dtype is CUXB_FLOAT16
+ *   (cux convention) or CUXB_FLOAT32.  Requires K % 8 == 0, N % 8 == 0, lda/ldb/ldc
+ *   multiples of 8 elements and 16-byte aligned base pointers (TMA). */
+int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const float *A,
+                   int lda, const float *B, int ldb, float beta, float *C, int ldc);
+int cuxb_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha,
+                          const void *A, int lda, const void *B, int ldb, float beta, void *C,
+                          int ldc, int c_dtype);
+
+/* ---- linear: C[M,N] = A[M,K] * Bt[N,K]^T (simd/x86/linear.cpp:2).
+ * cuxb_linear_s8_s32 replaces LinearNormalInt8 / LinearAvx512Int8
+ *   (simd/x86/linear.cpp:199-237): signed int8 x signed int8 -> int32, bit-exact.
+ * cuxb_linear_bf16_f32acc replaces LinearNormalBf16 / LinearAvx512Bf16
+ *   (simd/x86/linear.cpp:137-182); c_dtype CUXB_BFLOAT16 or CUXB_FLOAT32.
+ * cuxb_linear_f16_f32acc: the same contraction for fp16 inputs
+ *   (LinearAvx512AhBfCh, linear.cpp:186-196); c_dtype CUXB_FLOAT16 or CUXB_FLOAT32.
+ * Requires K % 16 == 0 bytes-aligned rows (K % 16 for int8, K % 8 for 16-bit). */
+int cuxb_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, int K, const int8_t *A,
+                       const int8_t *Bt, int32_t *C);
+int cuxb_linear_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A,
+                            const void *Bt, void *C, int c_dtype);
+int cuxb_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A,
+                           const void *Bt, void *C, int c_dtype);
+
+/* ---- element conversion on the device, replacing the scalar host loop
+ * Array4D::PrecsCpuCvt (0-frameworks/cux/include/array.h:124-144) for fp32 -> fp16/bf16
+ * (round to nearest even) and back. */
+int cuxb_convert(cuxb_ctx *ctx, void *stream, long long n, const void *src, int src_dtype, void *dst,
+                 int dst_dtype);
+
+/* ---- host-buffer entry points: what a cux plugin that is handed HOST arrays
+ * calls.  Inputs are copied host->device, the kernel runs, the result is
+ * copied back and the call returns after the stream has drained.  Pinned host
+ * memory (cuxb_malloc_host) makes the copies asynchronous DMA; pageable memory
+ * works but is slower.  Device staging buffers are owned by ctx and reused. */
+int cuxb_dot_f32_host(cuxb_ctx *ctx, long long n, const float *a, const float *b, float *res);
+int cuxb_sum_f32_host(cuxb_ctx *ctx, long long n, const float *x, float *res);
+int cuxb_nrm2_f32_host(cuxb_ctx *ctx, long long n, const float *x, float *res);
+int cuxb_scan_i32_host(cuxb_ctx *ctx, long long n, const int32_t *in, int32_t *out, int32_t seed);
+int cuxb_sgemm_f32_host(cuxb_ctx *ctx, int M, int N, int K, float alpha, const float *A, int lda,
+                        const float *B, int ldb, float beta, float *C, int ldc);
+int cuxb_hgemm_f16_f32acc_host(cuxb_ctx *ctx, int M, int N, int K, float alpha, const void *A,
+                               int lda, const void *B, int ldb, float beta, void *C, int ldc,
+                               int c_dtype);
+int cuxb_linear_s8_s32_host(cuxb_ctx *ctx, int M, int N, int K, const int8_t *A, const int8_t *Bt,
+                            int32_t *C);
+
+/* ---- occupancy hook, replacing Operator::QueryPotentialOccupancy on
+ * KernelIF::config_kernel (0-frameworks/cux/src/operator/operator.cpp:11-23).
+ * kernel: "dot_f32", "sum_f32", "nrm2_f32", "scan_i32", "sgemm_f32", "hgemm_f16". */
+int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *active_blocks_per_sm,
+                          double *occupancy, int *threads_per_block, int *dynamic_smem_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CUXB_H_ */

@@ -1,0 +1,100 @@
+"""GPU: the host-buffer entry points (what a cux plugin given host arrays calls), conversion and
+the occupancy hook."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from hpc_b200 import capi
+from hpc_b200 import datagen as dg
+from gpu_util import ctx, dev, host, sync
+
+pytestmark = pytest.mark.gpu
+
+
+def p(a):
+    return a.ctypes.data
+
+
+def test_dot_sum_nrm2_scan_host_buffers():
+    c = ctx()
+    n = 1_000_003
+    a, b = dg.int_fill(n, -2, 2, tag=1), dg.int_fill(n, -2, 2, tag=2)
+    r = np.zeros(1, np.float32)
+    c.dot_f32_host(n, p(a), p(b), p(r))
+    assert r[0] == oracle.dot_f32(a, b)
+    c.sum_f32_host(n, p(a), p(r))
+    assert r[0] == oracle.sum_f32(a)
+    c.nrm2_f32_host(n, p(a), p(r))
+    assert r[0] == oracle.nrm2_f32(a)
+    x = dg.int_fill(n, -2, 2, np.int32, tag=3)
+    out = np.empty_like(x)
+    c.scan_i32_host(n, p(x), p(out), 4)
+    assert np.array_equal(out, oracle.scan_i32(x, 4))
+
+
+def test_pinned_host_buffers():
+    L = capi.lib()
+    n = 1 << 20
+    hp = ctypes.c_void_p()
+    capi.check(L.cuxb_malloc_host(ctypes.byref(hp), n * 8 + 4))
+    buf = np.ctypeslib.as_array(ctypes.cast(hp, ctypes.POINTER(ctypes.c_float)), shape=(2 * n + 1,))
+    buf[:n] = dg.int_fill(n, -2, 2, tag=4)
+    buf[n:2 * n] = dg.int_fill(n, -2, 2, tag=5)
+    ctx().dot_f32_host(n, hp.value, hp.value + 4 * n, hp.value + 8 * n)
+    assert buf[2 * n] == oracle.dot_f32(buf[:n].copy(), buf[n:2 * n].copy())
+    capi.check(L.cuxb_free_host(hp))
+
+
+def test_gemm_host_buffers():
+    c = ctx()
+    M, N, K = 256, 384, 128
+    A, B, C = dg.int_fill((M, K), -2, 5, tag=6), dg.int_fill((K, N), -2, 5, tag=7), dg.int_fill((M, N), -2, 5, tag=8)
+    want = oracle.gemm_f32(A, B, C, 1.0, 3.0)
+    out = C.copy()
+    c.sgemm_f32_host(M, N, K, 1.0, p(A), K, p(B), N, 3.0, p(out), N)
+    assert np.array_equal(out, want)
+    A16, B16, C16 = oracle.f32_to_f16(A), oracle.f32_to_f16(B), oracle.f32_to_f16(C)
+    want16 = oracle.hgemm_f16(A16, B16, C16, 1.0, 3.0)
+    out16 = C16.copy()
+    c.hgemm_f16_host(M, N, K, 1.0, p(A16), K, p(B16), N, 3.0, p(out16), N)
+    assert np.array_equal(out16, want16)
+    A8, B8 = dg.int_fill((M, K), -128, 127, np.int8, tag=9), dg.int_fill((N, K), -128, 127, np.int8, tag=10)
+    out32 = np.empty((M, N), np.int32)
+    c.linear_s8_host(M, N, K, p(A8), p(B8), p(out32))
+    assert np.array_equal(out32, oracle.linear_s8(A8, B8))
+
+
+def test_device_convert_matches_rne_oracle():
+    c = ctx()
+    x = np.concatenate([dg.normal_fill(100000, tag=11) * s for s in (1e-7, 1e-3, 1.0, 3e4, 1e5)])
+    d = dev(x)
+    h = torch.empty(x.size, dtype=torch.int16, device="cuda")
+    c.convert(x.size, d.data_ptr(), capi.FLOAT32, h.data_ptr(), capi.FLOAT16)
+    sync()
+    assert np.array_equal(host(h, np.uint16), oracle.f32_to_f16(x))
+    c.convert(x.size, d.data_ptr(), capi.FLOAT32, h.data_ptr(), capi.BFLOAT16)
+    sync()
+    assert np.array_equal(host(h, np.uint16), oracle.f32_to_bf16(x))
+    back = torch.empty(x.size, dtype=torch.float32, device="cuda")
+    c.convert(x.size, h.data_ptr(), capi.BFLOAT16, back.data_ptr(), capi.FLOAT32)
+    sync()
+    assert np.array_equal(host(back), oracle.bf16_to_f32(oracle.f32_to_bf16(x)))
+
+
+def test_occupancy_hook_and_launch_counter():
+    c = ctx()
+    for k, th in (("dot_f32", 512), ("sum_f32", 512), ("nrm2_f32", 512), ("scan_i32", 256), ("sgemm_f32", 256),
+                  ("hgemm_f16", 256)):
+        ab, occ, threads, smem = c.occupancy(k)
+        assert ab >= 1 and 0 < occ <= 1 and threads == th, (k, ab, occ)
+    before = capi.launch_count()
+    out = torch.zeros(1, device="cuda")
+    x = torch.ones(1000, device="cuda")
+    c.sum_f32(1000, x.data_ptr(), out.data_ptr())
+    sync()
+    assert capi.launch_count() == before + 1 and float(out[0]) == 1000.0
+    with pytest.raises(capi.CuxbError):
+        c.occupancy("nope")
