@@ -106,7 +106,13 @@ def test_dot_full_size_2p28_bit_exact():
     da, db = dev(a), dev(b)
     assert run_red("dot", da, db) == oracle.dot_f32(a, b)
     assert run_red("sum", da) == oracle.sum_f32(a)
-    assert run_red("nrm2", da) == oracle.nrm2_f32(a)
+    # nrm2: sum(x^2) ~ 5.4e8 > 2^24, so the reference's own serial fp32 accumulation
+    # (Nrm2HostV0, nrm2.cpp:11-14) stagnates -- adding 1 stops at 2^24, adding 4 at 2^26 -- and it
+    # returns sqrt(2^26) = 8192 instead of ~23170.  Bit parity with a saturated sum is not a goal:
+    # the GPU result is checked against the fp64 truth (every x^2 and the total are exact integers).
+    truth = float(np.sqrt(np.sum(a.astype(np.float64) ** 2)))
+    assert oracle.nrm2_f32(a) == np.float32(8192.0)
+    assert abs(run_red("nrm2", da) - truth) <= 2 * EPS * truth
 
 
 # ------------------------------------------------------------------ scan
