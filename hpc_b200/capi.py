@@ -55,6 +55,7 @@ SIGNATURES = {
     "cuxb_sum_i32": ([_vp, _vp, _ll, _vp, _vp], _i),
     "cuxb_scan_i32": ([_vp, _vp, _ll, _vp, _vp, C.c_int32], _i),
     "cuxb_scan_f32": ([_vp, _vp, _ll, _vp, _vp, _f], _i),
+    "cuxb_scan_i32_noalloc": ([_vp, _ll, _vp, _vp, C.c_int32], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
     "cuxb_linear_s8_s32": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp], _i),

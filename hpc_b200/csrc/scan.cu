@@ -238,6 +238,37 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
 
 const void *scan_kernel_symbol() { return (const void *)scan_kernel<unsigned int>; }
 
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant (cuxb_scan_i32_noalloc).
+//
+// The scan needs scratch memory besides its input and output: one 64-bit state word per tile and
+// two counters.  The entry points above keep that scratch in the cuxb_ctx, which is created with
+// cudaMalloc and may grow it.  Some callers cannot do that: a plug-in that runs inside a host
+// application which has already handed all device memory to its own pool, a service with a fixed
+// memory budget where a late cudaMalloc may fail, or a latency-sensitive loop that cannot afford
+// the device-wide synchronisation an allocation implies.  For them the scratch lives in the
+// file-scope array below.  It is part of the library image, so every GPU that loads libcuxb.so
+// holds these ~128 KiB until the process exits, whether or not the entry point is ever called.
+//
+// Size limit: kNoAllocMaxElems elements (one state word per 4096-element tile).
+constexpr long long kNoAllocMaxElems = 1ll << 26;  // 67,108,864 int32 values = 256 MiB of input
+constexpr int kNoAllocMaxTiles = (int)(kNoAllocMaxElems / kScanTileElems);  // 16384 words = 128 KiB
+constexpr int kNoAllocCounterWords = 32;  // 256 bytes after the state words; [0],[1] are used
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + kNoAllocCounterWords];
+
+// Host-side bookkeeping, one slot per device ordinal.  `scratch` is the DEVICE address of
+// g_noalloc_scratch on that GPU: in host code the array's name is only a handle for the runtime,
+// not something a kernel can dereference, so the address is asked for once per device with
+// cudaGetSymbolAddress while that device is current.
+constexpr int kNoAllocMaxDevices = 64;
+struct NoAllocDevice {
+  unsigned long long *scratch;
+  unsigned int epoch;
+  bool ready;
+};
+static NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+static std::mutex g_noalloc_mu;
+
 }  // namespace cuxb
 
 using namespace cuxb;
@@ -250,4 +281,50 @@ CUXB_API int cuxb_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32
 CUXB_API int cuxb_scan_f32(cuxb_ctx *ctx, void *stream, long long n, const float *in, float *out,
                            float seed) {
   return scan_entry<float>("cuxb_scan_f32", ctx, stream, n, in, out, seed);
+}
+
+// See include/cuxb.h.  Works on the CURRENT device; takes no cuxb_ctx because creating one allocates.
+// Calls no cudaMalloc / cudaFree / allocating library routine.  The first call on each device looks
+// up the device address of the static scratch array (cudaGetSymbolAddress); make that first call
+// outside any stream capture.  All calls on one GPU share the same scratch: two calls whose kernels
+// overlap on that GPU (different streams, or different host threads) race on it and produce garbage.
+CUXB_API int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in, int32_t *out, int32_t seed) {
+  CUXB_REQUIRE(n >= 0, CUXB_ERR_INVALID, "cuxb_scan_i32_noalloc: negative length %lld", n);
+  CUXB_REQUIRE(n <= kNoAllocMaxElems, CUXB_ERR_TOO_LARGE,
+               "cuxb_scan_i32_noalloc: n=%lld is larger than the %lld elements the built-in scratch array covers; "
+               "use cuxb_scan_i32 (which allocates) or split the input and chain the pieces through `seed`",
+               n, kNoAllocMaxElems);
+  if (n == 0) return 0;
+  CUXB_REQUIRE(in && out, CUXB_ERR_INVALID, "cuxb_scan_i32_noalloc: null pointer");
+  int dev = -1;
+  CUXB_CUDA(cudaGetDevice(&dev));
+  CUXB_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, CUXB_ERR_UNSUPPORTED,
+               "cuxb_scan_i32_noalloc: device ordinal %d is outside the %d supported", dev, kNoAllocMaxDevices);
+  cudaStream_t st = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  NoAllocDevice &d = g_noalloc_dev[dev];
+  if (!d.ready) {
+    // one-time set-up for this GPU: resolve the array's device address (no allocation happens here)
+    unsigned long long *ptr = nullptr;
+    CUXB_CUDA(cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
+    CUXB_REQUIRE(ptr != nullptr, CUXB_ERR_UNSUPPORTED, "cuxb_scan_i32_noalloc: static scratch has no device address");
+    d.scratch = ptr;
+    d.epoch = 0;   // the array starts zero-filled, and no launch ever uses epoch 0
+    d.ready = true;
+  }
+  // The array still holds whatever the previous call left.  State words are told apart by the
+  // launch epoch, but the two tile counters must read zero when the kernel starts; a kernel that
+  // was aborted half-way would have left them set, so they are cleared on the stream every time.
+  unsigned int *counters = reinterpret_cast<unsigned int *>(d.scratch + kNoAllocMaxTiles);
+  CUXB_CUDA(cudaMemsetAsync(counters, 0, 2 * sizeof(unsigned int), st));
+  d.epoch = (d.epoch + 1) & 0x3fffffffu;
+  if (d.epoch == 0) {  // epoch wrapped after 2^30 calls: wipe the state words once and skip 0
+    CUXB_CUDA(cudaMemsetAsync(d.scratch, 0, (size_t)kNoAllocMaxTiles * sizeof(unsigned long long), st));
+    d.epoch = 1;
+  }
+  const unsigned int tiles = (unsigned int)div_up(n, kScanTileElems);
+  scan_kernel<unsigned int><<<tiles, kScanThreads, 0, st>>>((const unsigned int *)in, (unsigned int *)out, n,
+                                                            (unsigned int)seed, d.scratch, counters, d.epoch, tiles);
+  CUXB_LAUNCHED();
+  return 0;
 }

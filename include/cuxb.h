@@ -109,6 +109,15 @@ int cuxb_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *in, i
 /* fp32 variant (same recurrence; the order of additions differs from the serial
  * reference). */
 int cuxb_scan_f32(cuxb_ctx *ctx, void *stream, long long n, const float *in, float *out, float seed);
+/* The same int32 scan for callers that must not allocate device memory (a plug-in inside an
+ * application that owns all of the GPU's memory, a fixed-budget service, a loop that cannot take the
+ * device-wide stall of cudaMalloc).  It has no counterpart in the reference.  It takes no cuxb_ctx --
+ * creating one allocates -- and runs on the current device, keeping its tile-state scratch in a static
+ * array inside the library (about 128 KiB per GPU, held from library load to process exit).
+ * Limit: n <= 67,108,864 (2^26) elements; larger n returns CUXB_ERR_TOO_LARGE.  The first call on each
+ * device resolves the array's device address; make it before any stream capture starts.  Calls on the
+ * same GPU share the scratch, so two calls whose kernels may run at the same time race. */
+int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in, int32_t *out, int32_t seed);
 
 /* ---- GEMM: C = alpha * A[M,K] * B[K,N] + beta * C, row-major.
  *
