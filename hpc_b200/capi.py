@@ -41,6 +41,7 @@ SIGNATURES = {
     "cuxb_device_count": ([C.POINTER(_i)], _i),
     "cuxb_device_sync": ([], _i),
     "cuxb_device_name": ([_i, C.c_char_p, _sz], _i),
+    "cuxb_device_info": ([_i] + [C.POINTER(_i)] * 6 + [C.POINTER(_sz)] * 2, _i),
     "cuxb_stream_create": ([C.POINTER(_vp)], _i),
     "cuxb_stream_destroy": ([_vp], _i),
     "cuxb_stream_sync": ([_vp], _i),

@@ -167,6 +167,22 @@ CUXB_API int cuxb_device_name(int device, char *buf, size_t buflen) {
   return 0;
 }
 
+CUXB_API int cuxb_device_info(int device, int *sm_count, int *cc_major, int *cc_minor, int *max_threads_per_sm,
+                               int *max_threads_per_block, int *warp_size, size_t *global_mem_bytes,
+                               size_t *shared_mem_per_block) {
+  cudaDeviceProp prop;
+  CUXB_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (sm_count) *sm_count = prop.multiProcessorCount;
+  if (cc_major) *cc_major = prop.major;
+  if (cc_minor) *cc_minor = prop.minor;
+  if (max_threads_per_sm) *max_threads_per_sm = prop.maxThreadsPerMultiProcessor;
+  if (max_threads_per_block) *max_threads_per_block = prop.maxThreadsPerBlock;
+  if (warp_size) *warp_size = prop.warpSize;
+  if (global_mem_bytes) *global_mem_bytes = prop.totalGlobalMem;
+  if (shared_mem_per_block) *shared_mem_per_block = prop.sharedMemPerBlock;
+  return 0;
+}
+
 CUXB_API int cuxb_stream_create(void **s) {
   CUXB_REQUIRE(s, CUXB_ERR_INVALID, "null");
   cudaStream_t st;

@@ -32,7 +32,7 @@ public:
     if (decimal_pose > 0) {
       int s = 1;
       while (decimal_pose--) s *= 10;
-      for (int i = 0; i < len; i++) arr[i] += (float)(Next(st) % (uint32_t)s) / s;
+      for (int i = 0; i < len; i++) arr[i] = (DType)((float)arr[i] + (float)(Next(st) % (uint32_t)s) / s);
     }
   }
 };

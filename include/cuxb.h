@@ -73,6 +73,11 @@ int cuxb_set_device(int device);
 int cuxb_device_count(int *count);
 int cuxb_device_sync(void);
 int cuxb_device_name(int device, char *buf, size_t buflen);
+/* The cudaDeviceProp fields cux reads (0-frameworks/cux/include/executor.h:45-66,
+ * util/launch_config.h:56-58).  Any out pointer may be NULL. */
+int cuxb_device_info(int device, int *sm_count, int *cc_major, int *cc_minor, int *max_threads_per_sm,
+                     int *max_threads_per_block, int *warp_size, size_t *global_mem_bytes,
+                     size_t *shared_mem_per_block);
 
 /* ---- streams and events, replacing cux::GpuTimer
  * (0-frameworks/cux/include/util/timer.h:16-38). */

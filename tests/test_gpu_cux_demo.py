@@ -1,0 +1,36 @@
+"""GPU: the cux demo (hpc_b200/cux/example/demo.cpp) -- cux's own DotProductTest / Nrm2Test / GEMMTest
+flow (0-frameworks/cux/example/demo.cpp) plus the three added ops -- through Executor / OpFactory /
+plugins / Array4D over the C ABI.  Every ResultChecker verdict must be Pass and host kernel 0 must
+equal device kernel 0 bit for bit (integer-valued fills)."""
+import os
+import subprocess
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def run_demo(*args):
+    from hpc_b200 import build as b
+    from hpc_b200.cux import build as hb
+    b.build(verbose=False)
+    _, demo, _ = hb.build()
+    return subprocess.run([demo, *args], capture_output=True, text=True, timeout=600)
+
+
+def test_demo_reference_shapes():
+    r = run_demo()  # 4 096 000-element vectors, gemm 512x480x576 alpha=1 beta=3
+    out = r.stdout
+    assert r.returncode == 0, out[-3000:] + r.stderr[-2000:]
+    assert "cux_demo: all checks passed" in out
+    assert "Fail" not in out
+    for name in ("dot", "nrm2", "gemm fp32", "reduce_sum", "linear_int8", "scan_i32"):
+        assert "host V0 vs device V0 (%s): 0 of" % name in out, name
+    assert out.count("Pass: V0 vs V") >= 4  # plugin kernels and the fp16 tcgen05 kernel vs device V0
+    assert "tcgen05" in out and "Plugin example" in out
+
+
+def test_demo_quick():
+    r = run_demo("--quick")
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
