@@ -45,7 +45,7 @@ extern std::atomic<long long> g_launches;
 static inline long long div_up(long long a, long long b) { return (a + b - 1) / b; }
 
 // Scan tile-state capacity: one 64-bit word per tile.
-constexpr int kScanTileElems = 4096;                 // 256 threads x 16 ints
+constexpr int kScanTileElems = 8192;                 // 512 threads x 16 ints
 constexpr long long kScanMaxTiles = (1ll << 31) / kScanTileElems;  // n < 2^31 (cux uses int lengths)
 constexpr int kReduceMaxBlocks = 2048;
 

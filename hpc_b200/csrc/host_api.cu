@@ -13,6 +13,7 @@
 namespace cuxb {
 const void *reduce_kernel_symbol(const char *name);
 const void *scan_kernel_symbol();
+int scan_smem_bytes();
 const void *sgemm_kernel_symbol();
 const void *umma_kernel_symbol();
 int umma_smem_bytes();
@@ -148,7 +149,8 @@ CUXB_API int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *activ
   if ((fn = reduce_kernel_symbol(kernel)) != nullptr) {
     threads = 512;
   } else if (!strcmp(kernel, "scan_i32")) {
-    fn = scan_kernel_symbol(), threads = 256;
+    fn = scan_kernel_symbol(), threads = 512, smem = scan_smem_bytes();
+    CUXB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   } else if (!strcmp(kernel, "sgemm_f32")) {
     fn = sgemm_kernel_symbol(), threads = 256;
   } else if (!strcmp(kernel, "hgemm_f16")) {

@@ -6,28 +6,30 @@
 // uint32, i.e. two's-complement wrap-around, identical to the CPU oracle) and,
 // as a second instantiation, in fp32.
 //
-// One pass over the data ("decoupled look-back"): the input is cut into tiles
-// of 4096 elements; a CTA takes the next tile number from a global ticket (so
-// a CTA only ever waits on tiles that are already running), scans its tile in
-// registers (128-bit loads, shuffle scans), publishes the tile aggregate in a
-// 64-bit state word, then walks back over its predecessors' words -- 32 at a
-// time, one per lane -- until it meets one that already carries an inclusive
-// prefix.  value(32) | epoch(30) | status(2) share one word, so a single 64-bit
+// One pass over the data: the input is cut into tiles of 8192 elements; a persistent
+// grid of one resident CTA per SM walks the tiles round-robin (so a CTA only ever waits
+// on tiles owned by CTAs that are running).  cp.async streams tiles into a 128 KiB
+// shared-memory ring three passes ahead; a tile is scanned in registers (shuffle
+// scans), its aggregate is published in a 64-bit state word, and its exclusive prefix
+// is the CTA's own running prefix plus the aggregates of the tiles in between (see
+// "Prefix gathering" below) -- fetched one pass late so the L2 round trip is hidden.
+// value(32) | epoch(30) | status(2) share one word, so a single 64-bit
 // load observes a consistent (status, value) pair and the words never need
 // clearing between launches: a word from an older launch has a stale epoch and
 // reads as "not ready".
 //
-// Scratch memory: 8 bytes per tile (2 KiB per Mi elements) + two counters,
-// owned by the cuxb_ctx.  Launches that share a ctx must not overlap.
+// Scratch memory: 8 bytes per tile (1 KiB per Mi elements), owned by the
+// cuxb_ctx.  Launches that share a ctx must not overlap.
 #include "common.cuh"
 
 namespace cuxb {
 
-constexpr int kScanThreads = 256;
+constexpr int kScanThreads = 512;
 constexpr int kScanItems = 16;  // per thread: 4 x 128-bit
+constexpr int kScanCtasPerSM = 1;  // 128 KiB of shared memory per CTA
 static_assert(kScanThreads * kScanItems == kScanTileElems, "tile size");
 
-constexpr unsigned long long ST_AGG = 1ull, ST_PREFIX = 2ull;
+constexpr unsigned long long ST_AGG = 1ull;  // status field: 0 = not published (or stale epoch)
 
 __device__ __forceinline__ unsigned long long pack_state(unsigned int value, unsigned int epoch,
                                                          unsigned long long status) {
@@ -53,127 +55,107 @@ template <typename T> struct V4;
 template <> struct V4<unsigned int> { typedef uint4 type; };
 template <> struct V4<float> { typedef float4 type; };
 
-// Look-back executed by warp 0.  Returns the exclusive prefix of `tile` (seed included
-// through tile 0's published prefix).
+// ---------------------------------------------------------------------------------------------
+// Prefix gathering (warp 0).  With a persistent grid of G CTAs walking the tiles round-robin, the
+// tile G places back is this CTA's own previous tile, whose inclusive prefix it still holds in a
+// register.  A tile's exclusive prefix is that value plus the AGGREGATES of the (at most G-1)
+// tiles in between -- and every CTA publishes its aggregate before it looks at anybody else's, so
+// nothing ever waits on another CTA's look-back.  (The classic decoupled look-back waits for a
+// predecessor's full prefix; on a grid that runs in lock step that chains several L2 round trips
+// per pass and capped this kernel at ~2.8 TB/s.)  The loads for tile k are ISSUED in pass k and
+// CONSUMED in pass k+1, so their L2 round trip overlaps the scan of the next tile.
+constexpr int kGatherWords = 5;  // state words per lane: covers G-1 <= 160 predecessors in one round
+static_assert(kGatherWords * 32 >= 148 - 1, "one gather round must cover a B200's worth of CTAs");
+
 template <typename T>
-__device__ __forceinline__ T look_back(const unsigned long long *state, unsigned int tile,
-                                       unsigned int epoch) {
+struct Gather {
+  unsigned long long w[kGatherWords];
+  unsigned int tile, count;
+};
+
+template <typename T>
+__device__ __forceinline__ void gather_issue(Gather<T> &g, const unsigned long long *state, unsigned int tile,
+                                             unsigned int count) {
+  const int lane = threadIdx.x & 31;
+  g.tile = tile, g.count = count;
+#pragma unroll
+  for (int j = 0; j < kGatherWords; j++)
+    g.w[j] = ((unsigned)(j * 32 + lane) < count) ? ld_state(state + (tile - 1 - (j * 32 + lane))) : 0ull;
+}
+
+// Sum of the aggregates of tiles g.tile-1 ... g.tile-g.count, added in a fixed order.
+template <typename T>
+__device__ __forceinline__ T gather_finish(Gather<T> &g, const unsigned long long *state, unsigned int epoch) {
   const int lane = threadIdx.x & 31;
   const unsigned long long want_epoch = (unsigned long long)(epoch & 0x3fffffffu);
-  T running = 0;
-  long long pos = (long long)tile - 1;
-  while (true) {
-    const long long idx = pos - lane;
-    const bool valid = idx >= 0;  // lanes that fall before tile 0 contribute nothing
-    unsigned long long w = 0;
-    bool ready;
-    unsigned int spin = 0;
-    do {
-      if (valid) w = ld_state(state + idx);
-      ready = !valid || (((w & 3ull) != 0) && (((w >> 2) & 0x3fffffffull) == want_epoch));
-      if (++spin > 200000000u) __trap();  // a protocol bug must fail the launch, never hang the GPU
-    } while (!__all_sync(0xffffffffu, ready));
-    const bool is_prefix = valid && ((w & 3ull) == ST_PREFIX);
-    const unsigned int pm = __ballot_sync(0xffffffffu, is_prefix);
-    const T val = (idx >= 0) ? from_bits<T>((unsigned int)(w >> 32)) : (T)0;
-    // nearest predecessor with a full prefix: take it and every aggregate in front of it
-    const int stop = pm ? (__ffs(pm) - 1) : 31;
-    T contrib = (lane <= stop) ? val : (T)0;
-    // fixed-order fold across lanes (lane 0 = nearest tile)
+  T sum = 0;
+  for (unsigned int base = 0; base < g.count; base += 32 * kGatherWords) {  // one trip when G-1 <= 160
+    if (base) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
-    running += contrib;
-    if (pm) break;
-    pos -= 32;
+      for (int j = 0; j < kGatherWords; j++)
+        g.w[j] = (base + j * 32 + lane < g.count) ? ld_state(state + (g.tile - 1 - (base + j * 32 + lane))) : 0ull;
+    }
+    unsigned int spin = 0;
+    while (true) {
+      bool waiting = false;
+#pragma unroll
+      for (int j = 0; j < kGatherWords; j++) {
+        const bool mine = base + j * 32 + lane < g.count;
+        const bool ready = ((g.w[j] & 3ull) != 0) && (((g.w[j] >> 2) & 0x3fffffffull) == want_epoch);
+        if (mine && !ready) {
+          g.w[j] = ld_state(state + (g.tile - 1 - (base + j * 32 + lane)));  // poll again
+          waiting = true;
+        }
+      }
+      if (!__any_sync(0xffffffffu, waiting)) break;
+      if (++spin > 100000000u) __trap();  // a protocol bug must fail the launch, never hang the GPU
+    }
+#pragma unroll
+    for (int j = 0; j < kGatherWords; j++)
+      if (base + j * 32 + lane < g.count) sum += from_bits<T>((unsigned int)(g.w[j] >> 32));
   }
-  return running;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);  // fixed order
+  return sum;
+}
+
+// One tile = kScanTileElems consecutive elements; thread (warp w, lane l) owns, for j = 0..3, the
+// 4 elements at  w*512 + j*128 + l*4  -- every warp load/store instruction covers 512 contiguous bytes.
+template <typename T>
+struct TileRegs {
+  T v[4][4];
+};
+
+__device__ __forceinline__ long long tile_elem_base(unsigned int tile) {
+  return (long long)tile * kScanTileElems + (threadIdx.x >> 5) * 512 + (threadIdx.x & 31) * 4;
+}
+
+// Shared-memory ring: each thread keeps kScanRing private 64-byte slots; cp.async fills slot
+// (pass % kScanRing) kScanRing-1 passes ahead of use.  A slot is written and read by the same thread
+// only, so cp.async.wait_group is all the synchronisation it needs.  Layout [slot][j][thread] of
+// 16-byte chunks: conflict-free for both the async writes and the LDS.128 reads.
+constexpr int kScanRing = 4;
+constexpr int kScanSmemBytes = kScanRing * kScanTileElems * 4;  // 128 KiB
+
+template <typename T>
+__device__ __forceinline__ void prefetch_tile(uint4 *ring, int slot, const T *in, unsigned int tile) {
+  const long long base = tile_elem_base(tile);
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (slot * 4 + j) * kScanThreads + threadIdx.x);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(in + base + j * 128) : "memory");
+  }
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kScanThreads, 6)
-scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__restrict__ state,
-            unsigned int *__restrict__ counter, unsigned int epoch, unsigned int num_tiles) {
+__device__ __forceinline__ void store_tile(const TileRegs<T> &r, T add, T *out, long long n, unsigned int tile, bool vec_ok) {
   typedef typename V4<T>::type V;
-  __shared__ unsigned int s_tile;
-  __shared__ T s_warp[kScanThreads / 32];
-  __shared__ T s_prefix;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-  if (threadIdx.x == 0) s_tile = atomicAdd(&counter[0], 1u);
-  __syncthreads();
-  const unsigned int tile = s_tile;
-  const long long base = (long long)tile * kScanTileElems + warp * 512 + lane * 4;
-  const bool full = ((long long)(tile + 1) * kScanTileElems <= n) && ((((uintptr_t)in | (uintptr_t)out) & 15) == 0);
-
-  T v[4][4];
-  if (full) {
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      V t = __ldcs(reinterpret_cast<const V *>(in + base + j * 128));
-      v[j][0] = t.x, v[j][1] = t.y, v[j][2] = t.z, v[j][3] = t.w;
-    }
-  } else {
-#pragma unroll
-    for (int j = 0; j < 4; j++)
-#pragma unroll
-      for (int c = 0; c < 4; c++) {
-        const long long i = base + j * 128 + c;
-        v[j][c] = (i < n) ? in[i] : (T)0;
-      }
-  }
-
-  // thread-local inclusive scan of each 4-vector, then a shuffle scan per row j,
-  // rows chained through `carry`
-  T carry = 0;
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-    v[j][1] += v[j][0];
-    v[j][2] += v[j][1];
-    v[j][3] += v[j][2];
-    T incl = v[j][3];
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      T t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
-    }
-    T excl = __shfl_up_sync(0xffffffffu, incl, 1);
-    if (lane == 0) excl = 0;
-    const T off = carry + excl;
-#pragma unroll
-    for (int c = 0; c < 4; c++) v[j][c] += off;
-    carry += __shfl_sync(0xffffffffu, incl, 31);
-  }
-  if (lane == 31) s_warp[warp] = carry;
-  __syncthreads();
-
-  T warp_off = 0, block_total = 0;
-#pragma unroll
-  for (int w = 0; w < kScanThreads / 32; w++) {
-    const T t = s_warp[w];
-    if (w < warp) warp_off += t;
-    block_total += t;
-  }
-
-  if (warp == 0) {
-    T prefix;
-    if (tile == 0) {
-      prefix = seed;
-      if (lane == 0) st_state(state, pack_state(to_bits<T>(seed + block_total), epoch, ST_PREFIX));
-    } else {
-      if (lane == 0) st_state(state + tile, pack_state(to_bits<T>(block_total), epoch, ST_AGG));
-      prefix = look_back<T>(state, tile, epoch);
-      if (lane == 0) st_state(state + tile, pack_state(to_bits<T>(prefix + block_total), epoch, ST_PREFIX));
-    }
-    if (lane == 0) s_prefix = prefix;
-  }
-  __syncthreads();
-  const T add = s_prefix + warp_off;
-
-  if (full) {
+  const long long base = tile_elem_base(tile);
+  if (vec_ok && (long long)(tile + 1) * kScanTileElems <= n) {
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       V t;
-      t.x = v[j][0] + add, t.y = v[j][1] + add, t.z = v[j][2] + add, t.w = v[j][3] + add;
+      t.x = r.v[j][0] + add, t.y = r.v[j][1] + add, t.z = r.v[j][2] + add, t.w = r.v[j][3] + add;
       __stcs(reinterpret_cast<V *>(out + base + j * 128), t);
     }
   } else {
@@ -182,17 +164,133 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
 #pragma unroll
       for (int c = 0; c < 4; c++) {
         const long long i = base + j * 128 + c;
-        if (i < n) out[i] = v[j][c] + add;
+        if (i < n) out[i] = r.v[j][c] + add;
       }
   }
+}
 
-  // the last tile to finish puts both counters back to zero for the next launch
-  if (threadIdx.x == 0) {
-    const unsigned int done = atomicAdd(&counter[1], 1u);
-    if (done == num_tiles - 1) {
-      counter[0] = 0;
-      counter[1] = 0;
+// Persistent CTAs, one per SM: CTA b scans tiles b, b+G, b+2G, ... (G = gridDim.x; every CTA is
+// resident, which is what makes waiting on another CTA's aggregate safe).  Three things overlap:
+//   * cp.async streams tiles into the shared-memory ring three passes ahead (96 KiB in flight per SM);
+//   * the scan of tile k (registers: shuffle scans, one __syncthreads for the warp totals);
+//   * the L2 round trip that fetches the other CTAs' aggregates for tile k -- issued in pass k,
+//     consumed in pass k+1 together with the store of tile k.
+// `counter` is unused (kept for the callers' scratch layout).
+template <typename T>
+__global__ void __launch_bounds__(kScanThreads, 1)
+scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__restrict__ state,
+            unsigned int *__restrict__ counter, unsigned int epoch, unsigned int num_tiles) {
+  (void)counter;
+  typedef typename V4<T>::type V;
+  extern __shared__ __align__(16) unsigned char scan_smem[];
+  uint4 *ring = reinterpret_cast<uint4 *>(scan_smem);
+  __shared__ T s_warp[2][kScanThreads / 32];
+  __shared__ T s_prefix[2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool vec_ok = ((((uintptr_t)in | (uintptr_t)out) & 15) == 0);
+  const unsigned int G = gridDim.x;
+  const unsigned int first_tile = blockIdx.x;
+  if (first_tile >= num_tiles) return;
+  auto is_async = [&](unsigned int t) { return vec_ok && t < num_tiles && (long long)(t + 1) * kScanTileElems <= n; };
+
+  // prologue: fill the ring kScanRing-1 tiles deep (one commit group per pass, even when empty,
+  // so that wait_group counts passes)
+#pragma unroll
+  for (int d = 0; d < kScanRing - 1; d++) {
+    const unsigned int t = first_tile + d * G;
+    if (is_async(t)) prefetch_tile(ring, d, in, t);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+
+  TileRegs<T> cur, prv;
+  Gather<T> pend;           // warp 0: aggregate loads in flight for the previous tile
+  pend.count = 0, pend.tile = 0;
+  T running = 0;            // warp 0: inclusive prefix of the last tile this CTA finished
+  T prv_warp_off = 0, prv_total = 0;
+  unsigned int prv_tile = 0;
+  bool have_prv = false;
+  unsigned int pass = 0;
+  for (unsigned int tile = first_tile; tile < num_tiles; tile += G, pass++) {
+    const int par = pass & 1;
+    {  // keep the ring full
+      const unsigned int t = tile + (kScanRing - 1) * G;
+      if (is_async(t)) prefetch_tile(ring, (pass + kScanRing - 1) % kScanRing, in, t);
+      asm volatile("cp.async.commit_group;" ::: "memory");
     }
+    // ---- fetch this tile into registers
+    if (is_async(tile)) {
+      asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing - 1) : "memory");
+      const int slot = pass % kScanRing;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const V t = *reinterpret_cast<const V *>(ring + (slot * 4 + j) * kScanThreads + threadIdx.x);
+        cur.v[j][0] = t.x, cur.v[j][1] = t.y, cur.v[j][2] = t.z, cur.v[j][3] = t.w;
+      }
+    } else {  // ragged last tile or unaligned pointers: guarded scalar loads
+      const long long base = tile_elem_base(tile);
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+          const long long i = base + j * 128 + c;
+          cur.v[j][c] = (i < n) ? in[i] : (T)0;
+        }
+    }
+
+    // ---- scan the tile: thread-local, then a shuffle scan per row j, rows chained through `carry`
+    T carry = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      cur.v[j][1] += cur.v[j][0];
+      cur.v[j][2] += cur.v[j][1];
+      cur.v[j][3] += cur.v[j][2];
+      T incl = cur.v[j][3];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const T t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      T excl = __shfl_up_sync(0xffffffffu, incl, 1);
+      if (lane == 0) excl = 0;
+      const T off = carry + excl;
+#pragma unroll
+      for (int c = 0; c < 4; c++) cur.v[j][c] += off;
+      carry += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane == 31) s_warp[par][warp] = carry;
+    __syncthreads();  // (A) warp totals of this pass visible; s_prefix of the previous pass consumed
+
+    T warp_off = 0, block_total = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; w++) {
+      const T t = s_warp[par][w];
+      if (w < warp) warp_off += t;
+      block_total += t;
+    }
+
+    if (warp == 0) {
+      // publish this tile's aggregate, then settle the PREVIOUS tile and start fetching for this one
+      if (lane == 0) st_state(state + tile, pack_state(to_bits<T>(block_total), epoch, ST_AGG));
+      if (have_prv) {
+        const T prefix = ((prv_tile < G) ? seed : running) + gather_finish<T>(pend, state, epoch);
+        if (lane == 0) s_prefix[par] = prefix;
+        running = prefix + prv_total;
+      }
+      gather_issue<T>(pend, state, tile, (tile < G) ? tile : G - 1);
+    }
+    __syncthreads();  // (B) prefix of the previous tile visible
+    if (have_prv) store_tile(prv, s_prefix[par] + prv_warp_off, out, n, prv_tile, vec_ok);
+    prv = cur, prv_warp_off = warp_off, prv_tile = tile, have_prv = true;
+    prv_total = block_total;
+  }
+  // epilogue: settle and store the last tile
+  if (have_prv) {
+    if (warp == 0) {
+      const T prefix = ((prv_tile < G) ? seed : running) + gather_finish<T>(pend, state, epoch);
+      if (lane == 0) s_prefix[0] = prefix;
+    }
+    __syncthreads();
+    store_tile(prv, s_prefix[0] + prv_warp_off, out, n, prv_tile, vec_ok);
   }
 }
 
@@ -229,20 +327,23 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
     CUXB_CUDA(cudaMemsetAsync(ctx->scan_state, 0, ctx->scan_state_tiles * sizeof(unsigned long long), st));
     ctx->scan_epoch = 1;
   }
-  scan_kernel<T><<<(unsigned int)tiles, kScanThreads, 0, st>>>(in, out, n, seed, ctx->scan_state,
-                                                                ctx->scan_counter, ctx->scan_epoch,
-                                                                (unsigned int)tiles);
+  long long grid = (long long)ctx->sm_count * kScanCtasPerSM;  // all CTAs resident (see scan_kernel)
+  if (grid > tiles) grid = tiles;
+  CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
+  scan_kernel<T><<<(unsigned int)grid, kScanThreads, kScanSmemBytes, st>>>(in, out, n, seed, ctx->scan_state,
+                                                               ctx->scan_counter, ctx->scan_epoch,
+                                                               (unsigned int)tiles);
   CUXB_LAUNCHED();
   return 0;
 }
 
 const void *scan_kernel_symbol() { return (const void *)scan_kernel<unsigned int>; }
+int scan_smem_bytes() { return kScanSmemBytes; }
 
 // ---------------------------------------------------------------------------------------------
 // Allocation-free variant (cuxb_scan_i32_noalloc).
 //
-// The scan needs scratch memory besides its input and output: one 64-bit state word per tile and
-// two counters.  The entry points above keep that scratch in the cuxb_ctx, which is created with
+// The scan needs scratch memory besides its input and output: one 64-bit state word per tile.  The entry points above keep that scratch in the cuxb_ctx, which is created with
 // cudaMalloc and may grow it.  Some callers cannot do that: a plug-in that runs inside a host
 // application which has already handed all device memory to its own pool, a service with a fixed
 // memory budget where a late cudaMalloc may fail, or a latency-sensitive loop that cannot afford
@@ -250,9 +351,11 @@ const void *scan_kernel_symbol() { return (const void *)scan_kernel<unsigned int
 // file-scope array below.  It is part of the library image, so every GPU that loads libcuxb.so
 // holds these ~128 KiB until the process exits, whether or not the entry point is ever called.
 //
-// Size limit: kNoAllocMaxElems elements (one state word per 4096-element tile).
+// Size limit: kNoAllocMaxElems elements.  The array holds one state word per 4096 elements of that
+// limit; the kernel's tiles are at least that large, so a call uses a prefix of the array.
 constexpr long long kNoAllocMaxElems = 1ll << 26;  // 67,108,864 int32 values = 256 MiB of input
-constexpr int kNoAllocMaxTiles = (int)(kNoAllocMaxElems / kScanTileElems);  // 16384 words = 128 KiB
+constexpr int kNoAllocMaxTiles = (int)(kNoAllocMaxElems / 4096);  // 16384 words = 128 KiB
+static_assert(kScanTileElems >= 4096, "the static scratch is sized for tiles of at least 4096 elements");
 constexpr int kNoAllocCounterWords = 32;  // 256 bytes after the state words; [0],[1] are used
 static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + kNoAllocCounterWords];
 
@@ -264,6 +367,7 @@ constexpr int kNoAllocMaxDevices = 64;
 struct NoAllocDevice {
   unsigned long long *scratch;
   unsigned int epoch;
+  int sm_count;
   bool ready;
 };
 static NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
@@ -308,22 +412,26 @@ CUXB_API int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in,
     unsigned long long *ptr = nullptr;
     CUXB_CUDA(cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
     CUXB_REQUIRE(ptr != nullptr, CUXB_ERR_UNSUPPORTED, "cuxb_scan_i32_noalloc: static scratch has no device address");
+    CUXB_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
     d.scratch = ptr;
     d.epoch = 0;   // the array starts zero-filled, and no launch ever uses epoch 0
     d.ready = true;
   }
-  // The array still holds whatever the previous call left.  State words are told apart by the
-  // launch epoch, but the two tile counters must read zero when the kernel starts; a kernel that
-  // was aborted half-way would have left them set, so they are cleared on the stream every time.
-  unsigned int *counters = reinterpret_cast<unsigned int *>(d.scratch + kNoAllocMaxTiles);
-  CUXB_CUDA(cudaMemsetAsync(counters, 0, 2 * sizeof(unsigned int), st));
+  // The array still holds whatever the previous call left.  Nothing has to be cleared for that:
+  // every state word carries the epoch of the launch that wrote it, this launch gets a fresh epoch,
+  // and a word with any other epoch reads as "not published yet".  Only when the 30-bit epoch wraps
+  // are the words wiped (on the caller's stream, ahead of the kernel).
+  unsigned int *counters = reinterpret_cast<unsigned int *>(d.scratch + kNoAllocMaxTiles);  // reserved, unused
   d.epoch = (d.epoch + 1) & 0x3fffffffu;
   if (d.epoch == 0) {  // epoch wrapped after 2^30 calls: wipe the state words once and skip 0
     CUXB_CUDA(cudaMemsetAsync(d.scratch, 0, (size_t)kNoAllocMaxTiles * sizeof(unsigned long long), st));
     d.epoch = 1;
   }
   const unsigned int tiles = (unsigned int)div_up(n, kScanTileElems);
-  scan_kernel<unsigned int><<<tiles, kScanThreads, 0, st>>>((const unsigned int *)in, (unsigned int *)out, n,
+  unsigned int grid = (unsigned int)d.sm_count * kScanCtasPerSM;  // every CTA resident at once
+  if (grid > tiles) grid = tiles;
+  CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<unsigned int>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
+  scan_kernel<unsigned int><<<grid, kScanThreads, kScanSmemBytes, st>>>((const unsigned int *)in, (unsigned int *)out, n,
                                                             (unsigned int)seed, d.scratch, counters, d.epoch, tiles);
   CUXB_LAUNCHED();
   return 0;

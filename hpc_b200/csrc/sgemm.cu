@@ -7,11 +7,12 @@
 //
 //   CTA tile 128x128x16, 256 threads (8 warps as 2x4), 8x8 register micro-tile
 //   per thread split 4+4 in both directions so that every shared-memory read is
-//   a conflict-free LDS.128 whose 32 lanes touch only 128 (A) / 64 (B) distinct
-//   bytes -- 4 LDS.128 feed 64 FFMA.
+//   a conflict-free LDS.128 at the hardware minimum of 2 wavefronts -- 4 LDS.128
+//   (8 wavefronts) feed 64 FFMA.
 //   A is stored k-major (transposed) in shared memory, B as it lies.
-//   Global->shared goes through registers (LDG.128 for tile t+1 is issued before
-//   the FFMA block of tile t and stored after it), two shared-memory stages, one
+//   Tile t+1 is fetched while tile t is multiplied: B with cp.async straight into
+//   the other shared-memory stage, A with LDG.128 into registers (issued before
+//   the FFMA block, transposed into shared memory after it); two stages, one
 //   __syncthreads per k-tile.  Register fragments are double-buffered inside the
 //   tile.  CTAs are rasterised in groups of 8 tile-rows so that the B panel a
 //   wave needs stays in the 126 MB L2.
@@ -50,7 +51,11 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   const int tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   const int warp_m = warp >> 2, warp_n = warp & 3;   // 2 x 4 warps
-  const int lane_m = lane >> 2, lane_n = lane & 3;   // 8 x 4 lanes
+  // 8 x 4 lanes.  An LDS.128 costs max(2, distinct 16-byte chunks per 4-lane group) wavefronts
+  // (measured on B200, tools/lds_patterns.cu), so within every group of four consecutive lanes the
+  // A index may take two values (lane bit 1) and the B index two values (lane bit 0): both
+  // fragment loads then cost the minimum of 2 wavefronts.
+  const int lane_m = (lane >> 1) & 7, lane_n = ((lane & 16) >> 3) | (lane & 1);
   // rows owned: tm0 + {0..3} and tm0 + 32 + {0..3};  cols: tn0 + {0..3} and tn0 + 16 + {0..3}
   const int tm0 = warp_m * 64 + lane_m * 4;
   const int tn0 = warp_n * 32 + lane_n * 4;
@@ -70,30 +75,36 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   const int b_k = tid >> 5, b_n4 = (tid & 31) * 4;   // + 8*i k-rows
 
   float4 ra[2], rb[2];
-  auto gload = [&](int k0) {
+  // ---- global -> registers / shared.  FAST: B goes straight to shared memory with cp.async (no
+  // staging registers), A through registers because it is transposed on the way.  The loads are
+  // volatile asm with a memory clobber so they are ISSUED here, ahead of the FFMA block of the
+  // current tile (left to itself the compiler sinks them next to the stores and exposes the full
+  // global-memory latency once per k-tile).
+  auto gload = [&](int k0, int nbuf) {
 #pragma unroll
     for (int i = 0; i < 2; i++) {
       const int m = m_base + a_row + 64 * i;
       const int k = k0 + a_k4;
+      const int kb = k0 + b_k + 8 * i;
+      const int n = n_base + b_n4;
       if (FAST) {
-        ra[i] = __ldg(reinterpret_cast<const float4 *>(p.A + (size_t)m * p.lda + k));
+        const float *ap = p.A + (size_t)m * p.lda + k;
+        asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(ra[i].x), "=f"(ra[i].y), "=f"(ra[i].z), "=f"(ra[i].w) : "l"(ap) : "memory");
+        const float *bp = p.B + (size_t)kb * p.ldb + n;
+        const unsigned sdst = (unsigned)__cvta_generic_to_shared(&Bs[nbuf][b_k + 8 * i][b_n4]);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(bp) : "memory");
       } else {
         float t[4];
 #pragma unroll
         for (int c = 0; c < 4; c++) t[c] = (m < p.M && k + c < p.K) ? p.A[(size_t)m * p.lda + k + c] : 0.f;
         ra[i] = make_float4(t[0], t[1], t[2], t[3]);
-      }
-      const int kb = k0 + b_k + 8 * i;
-      const int n = n_base + b_n4;
-      if (FAST) {
-        rb[i] = __ldg(reinterpret_cast<const float4 *>(p.B + (size_t)kb * p.ldb + n));
-      } else {
-        float t[4];
 #pragma unroll
         for (int c = 0; c < 4; c++) t[c] = (kb < p.K && n + c < p.N) ? p.B[(size_t)kb * p.ldb + n + c] : 0.f;
         rb[i] = make_float4(t[0], t[1], t[2], t[3]);
       }
     }
+    if (FAST) asm volatile("cp.async.commit_group;" ::: "memory");
   };
   auto sstore = [&](int buf) {
 #pragma unroll
@@ -103,8 +114,9 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
       As[buf][a_k4 + 1][m] = ra[i].y;
       As[buf][a_k4 + 2][m] = ra[i].z;
       As[buf][a_k4 + 3][m] = ra[i].w;
-      *reinterpret_cast<float4 *>(&Bs[buf][b_k + 8 * i][b_n4]) = rb[i];
+      if (!FAST) *reinterpret_cast<float4 *>(&Bs[buf][b_k + 8 * i][b_n4]) = rb[i];
     }
+    if (FAST) asm volatile("cp.async.wait_group 0;" ::: "memory");
   };
 
   float acc[8][8];
@@ -114,7 +126,7 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
     for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
 
   const int KT = (p.K + SG_BK - 1) / SG_BK;
-  gload(0);
+  gload(0, 0);
   sstore(0);
   __syncthreads();
 
@@ -133,7 +145,7 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   for (int kt = 0; kt < KT; kt++) {
     const int buf = kt & 1;
     const bool more = kt + 1 < KT;
-    if (more) gload((kt + 1) * SG_BK);
+    if (more) gload((kt + 1) * SG_BK, buf ^ 1);
     lfrag(buf, 0, 0);
 #pragma unroll
     for (int k = 0; k < SG_BK; k++) {

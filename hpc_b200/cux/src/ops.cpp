@@ -568,12 +568,13 @@ ScanI32::ScanI32(OpAssistor *assistor) : Operator(assistor) {
     auto *k = new ScanGpuKernelIF();
     OpAssistor *as = assistor_;
     k->type_flag = TypeFlag::INT32;
-    k->describe_info = "cuxb sm_100a: single-pass scan, 4096-element tiles, decoupled look-back";
+    k->describe_info = "cuxb sm_100a: single-pass scan: one persistent CTA per SM, cp.async ring, 8192-element tiles, aggregate gathering";
     k->get_config = [](int n) {
       Config1D c;
       c.virtual_thread_count = n;
-      c.threads_per_block = 256;
-      c.blocks_per_grid = DivUp(n, 4096);
+      c.threads_per_block = 512;
+      c.blocks_per_grid = std::min(DivUp(n, 8192), 148);
+      c.shared_memory_size = 128 * 1024;
       return c;
     };
     k->func = [as](Config1D, int n, const void *in, void *out) {

@@ -125,7 +125,7 @@ def run_scan(x, seed=0, inplace=False):
     return host(out)
 
 
-@pytest.mark.parametrize("n", [1, 5, 4095, 4096, 4097, 100000, (1 << 22) + 17, 12345678])
+@pytest.mark.parametrize("n", [1, 5, 4095, 4096, 4097, 8191, 8192, 8193, 100000, (1 << 22) + 17, 12345678])
 def test_scan_i32_bit_exact(n):
     x = dg.int_fill(n, -2, 2, np.int32, tag=n)
     assert np.array_equal(run_scan(x), oracle.scan_i32(x))
