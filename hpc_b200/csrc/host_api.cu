@@ -149,7 +149,7 @@ CUXB_API int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *activ
   if ((fn = reduce_kernel_symbol(kernel)) != nullptr) {
     threads = 512;
   } else if (!strcmp(kernel, "scan_i32")) {
-    fn = scan_kernel_symbol(), threads = 512, smem = scan_smem_bytes();
+    fn = scan_kernel_symbol(), threads = 512 + 32, smem = scan_smem_bytes();
     CUXB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   } else if (!strcmp(kernel, "sgemm_f32")) {
     fn = sgemm_kernel_symbol(), threads = 256;

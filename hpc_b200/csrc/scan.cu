@@ -24,7 +24,7 @@
 
 namespace cuxb {
 
-constexpr int kScanThreads = 512;
+constexpr int kScanThreads = kScanTileElems / 16;
 constexpr int kScanItems = 16;  // per thread: 4 x 128-bit
 constexpr int kScanCtasPerSM = 1;  // 128 KiB of shared memory per CTA
 static_assert(kScanThreads * kScanItems == kScanTileElems, "tile size");
@@ -62,10 +62,11 @@ template <> struct V4<float> { typedef float4 type; };
 // tiles in between -- and every CTA publishes its aggregate before it looks at anybody else's, so
 // nothing ever waits on another CTA's look-back.  (The classic decoupled look-back waits for a
 // predecessor's full prefix; on a grid that runs in lock step that chains several L2 round trips
-// per pass and capped this kernel at ~2.8 TB/s.)  The loads for tile k are ISSUED in pass k and
-// CONSUMED in pass k+1, so their L2 round trip overlaps the scan of the next tile.
+// per pass and capped this kernel at ~2.8 TB/s.)  The aggregates for tile k are fetched at the
+// top of pass k+1 -- by then every CTA has published them -- and consumed at the end of that pass
+// together with the store of tile k, so the L2 round trip overlaps the scan of tile k+1.
 constexpr int kGatherWords = 5;  // state words per lane: covers G-1 <= 160 predecessors in one round
-static_assert(kGatherWords * 32 >= 148 - 1, "one gather round must cover a B200's worth of CTAs");
+static_assert(kGatherWords * 32 >= 148 * kScanCtasPerSM - 1, "one gather round must cover a B200's worth of CTAs");
 
 template <typename T>
 struct Gather {
@@ -127,16 +128,13 @@ struct TileRegs {
 };
 
 __device__ __forceinline__ long long tile_elem_base(unsigned int tile) {
-  return (long long)tile * kScanTileElems + (threadIdx.x >> 5) * 512 + (threadIdx.x & 31) * 4;
+  return (long long)tile * kScanTileElems + (threadIdx.x >> 5) * 512 + (threadIdx.x & 31) * 4;  // warp w: 512 elements
 }
 
-// Shared-memory ring: each thread keeps kScanRing private 64-byte slots; cp.async fills slot
-// (pass % kScanRing) kScanRing-1 passes ahead of use.  A slot is written and read by the same thread
-// only, so cp.async.wait_group is all the synchronisation it needs.  Layout [slot][j][thread] of
-// 16-byte chunks: conflict-free for both the async writes and the LDS.128 reads.
-constexpr int kScanRing = 4;
-constexpr int kScanSmemBytes = kScanRing * kScanTileElems * 4;  // 128 KiB
-
+// Shared-memory ring (kScanRing tile slots, see the pipeline description further down): every scan
+// thread owns the same four 16-byte chunks of each slot -- filled by its own cp.async, read, rewritten
+// and read again by itself only.  Layout [slot][j][thread]: conflict-free for the async writes and for
+// LDS.128 / STS.128.
 template <typename T>
 __device__ __forceinline__ void prefetch_tile(uint4 *ring, int slot, const T *in, unsigned int tile) {
   const long long base = tile_elem_base(tile);
@@ -169,15 +167,34 @@ __device__ __forceinline__ void store_tile(const TileRegs<T> &r, T add, T *out, 
   }
 }
 
+// Named barriers (barrier 0 is left to __syncthreads).
+__device__ __forceinline__ void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+constexpr int kScanCtaThreads = kScanThreads + 32;  // 16 scan warps + 1 helper warp
+constexpr int BAR_TOTALS = 1;                        // warp totals of a tile are in shared memory
+constexpr int BAR_PREFIX = 2;                        // (+ pass % 4) the tile's exclusive prefix is in shared memory
+
+// Software pipeline, in passes (one tile per CTA per pass):
+//   pass p - kPrefetch : cp.async of tile p into its ring slot starts
+//   pass p             : scan warps scan tile p in registers, park the scanned values in the slot,
+//                        publish the warp totals; the helper warp publishes the tile AGGREGATE
+//   pass p + kGatherLag: the helper fetches the other CTAs' aggregates for tile p (published two
+//                        passes ago, so the loads come back ready) -> exclusive prefix of tile p
+//   pass p + kStoreLag : scan warps add the prefix and store tile p; its slot is free again
+constexpr int kPrefetch = 2, kGatherLag = 2, kStoreLag = 3;
+constexpr int kScanRing = 6;
+static_assert(kScanRing >= kPrefetch + kStoreLag + 1, "a slot must be stored before it is refilled");
+constexpr int kScanSmemBytes = kScanRing * kScanTileElems * 4;  // 192 KiB
+
 // Persistent CTAs, one per SM: CTA b scans tiles b, b+G, b+2G, ... (G = gridDim.x; every CTA is
-// resident, which is what makes waiting on another CTA's aggregate safe).  Three things overlap:
-//   * cp.async streams tiles into the shared-memory ring three passes ahead (96 KiB in flight per SM);
-//   * the scan of tile k (registers: shuffle scans, one __syncthreads for the warp totals);
-//   * the L2 round trip that fetches the other CTAs' aggregates for tile k -- issued in pass k,
-//     consumed in pass k+1 together with the store of tile k.
+// resident, which is what makes waiting on another CTA's aggregate safe).  Roles:
+//   * 16 scan warps: each thread owns the same four 16-byte chunks of every ring slot (filled by
+//     its own cp.async, so cp.async.wait_group is all the synchronisation the data needs).
+//   * 1 helper warp: aggregate publication and prefix gathering; its L2 round trips never sit on
+//     the scan warps' critical path.
 // `counter` is unused (kept for the callers' scratch layout).
 template <typename T>
-__global__ void __launch_bounds__(kScanThreads, 1)
+__global__ void __launch_bounds__(kScanCtaThreads, 1)
 scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__restrict__ state,
             unsigned int *__restrict__ counter, unsigned int epoch, unsigned int num_tiles) {
   (void)counter;
@@ -185,49 +202,96 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
   extern __shared__ __align__(16) unsigned char scan_smem[];
   uint4 *ring = reinterpret_cast<uint4 *>(scan_smem);
   __shared__ T s_warp[2][kScanThreads / 32];
-  __shared__ T s_prefix[2];
+  __shared__ T s_prefix[4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const bool vec_ok = ((((uintptr_t)in | (uintptr_t)out) & 15) == 0);
   const unsigned int G = gridDim.x;
   const unsigned int first_tile = blockIdx.x;
   if (first_tile >= num_tiles) return;
-  auto is_async = [&](unsigned int t) { return vec_ok && t < num_tiles && (long long)(t + 1) * kScanTileElems <= n; };
+  const int passes = (int)((num_tiles - first_tile + G - 1) / G);  // tiles this CTA owns
 
-  // prologue: fill the ring kScanRing-1 tiles deep (one commit group per pass, even when empty,
-  // so that wait_group counts passes)
+  if (warp == kScanThreads / 32) {
+    // ===================================== helper warp =====================================
+    T running = 0;          // inclusive prefix of the last tile whose prefix was settled
+    T hist[kGatherLag + 1];  // block totals of the most recent passes, hist[0] = current
 #pragma unroll
-  for (int d = 0; d < kScanRing - 1; d++) {
-    const unsigned int t = first_tile + d * G;
-    if (is_async(t)) prefetch_tile(ring, d, in, t);
+    for (int i = 0; i <= kGatherLag; i++) hist[i] = 0;
+    auto settle = [&](int q, T total_q) {
+      const unsigned int tile = first_tile + (unsigned int)q * G;
+      Gather<T> g;
+      const bool first = tile < G;
+      gather_issue<T>(g, state, tile, first ? tile : G - 1);
+      const T prefix = (first ? seed : running) + gather_finish<T>(g, state, epoch);
+      running = prefix + total_q;
+      if (lane == 0) s_prefix[q & 3] = prefix;
+      __threadfence_block();
+      named_bar_arrive(BAR_PREFIX + (q & 3), kScanCtaThreads);
+    };
+    for (int p = 0; p < passes; p++) {
+      named_bar_sync(BAR_TOTALS, kScanCtaThreads);
+#pragma unroll
+      for (int i = kGatherLag; i > 0; i--) hist[i] = hist[i - 1];
+      T total = 0;
+#pragma unroll
+      for (int w = 0; w < kScanThreads / 32; w++) total += s_warp[p & 1][w];
+      hist[0] = total;
+      if (lane == 0) st_state(state + first_tile + (unsigned int)p * G, pack_state(to_bits<T>(total), epoch, ST_AGG));
+      if (p >= kGatherLag) settle(p - kGatherLag, hist[kGatherLag]);
+    }
+    // drain: the last kGatherLag tiles
+#pragma unroll
+    for (int d = kGatherLag; d > 0; d--) {
+      const int q = passes - d;
+      if (q >= 0) settle(q, hist[d - 1]);
+    }
+    return;
+  }
+
+  // ======================================= scan warps =======================================
+  auto tile_of = [&](int q) { return first_tile + (unsigned int)q * G; };
+  auto is_async = [&](int q) {
+    return vec_ok && q < passes && (long long)(tile_of(q) + 1) * kScanTileElems <= n;
+  };
+  auto slot_ptr = [&](int q, int j) { return ring + ((q % kScanRing) * 4 + j) * kScanThreads + threadIdx.x; };
+  // add the settled prefix to a parked tile and write it out
+  auto finish_tile = [&](int q, T warp_off_q) {
+    named_bar_sync(BAR_PREFIX + (q & 3), kScanCtaThreads);
+    const T add = s_prefix[q & 3] + warp_off_q;
+    TileRegs<T> r;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const V t = *reinterpret_cast<const V *>(slot_ptr(q, j));
+      r.v[j][0] = t.x, r.v[j][1] = t.y, r.v[j][2] = t.z, r.v[j][3] = t.w;
+    }
+    store_tile(r, add, out, n, tile_of(q), vec_ok);
+  };
+
+  // prologue: start the first kPrefetch tiles (one commit group per pass, even when empty, so
+  // that wait_group counts passes)
+#pragma unroll
+  for (int d = 0; d < kPrefetch; d++) {
+    if (is_async(d)) prefetch_tile(ring, d % kScanRing, in, tile_of(d));
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
 
-  TileRegs<T> cur, prv;
-  Gather<T> pend;           // warp 0: aggregate loads in flight for the previous tile
-  pend.count = 0, pend.tile = 0;
-  T running = 0;            // warp 0: inclusive prefix of the last tile this CTA finished
-  T prv_warp_off = 0, prv_total = 0;
-  unsigned int prv_tile = 0;
-  bool have_prv = false;
-  unsigned int pass = 0;
-  for (unsigned int tile = first_tile; tile < num_tiles; tile += G, pass++) {
-    const int par = pass & 1;
-    {  // keep the ring full
-      const unsigned int t = tile + (kScanRing - 1) * G;
-      if (is_async(t)) prefetch_tile(ring, (pass + kScanRing - 1) % kScanRing, in, t);
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    }
+  T woff[kStoreLag + 1];  // warp offsets of the tiles still parked in the ring, woff[0] = current
+#pragma unroll
+  for (int i = 0; i <= kStoreLag; i++) woff[i] = 0;
+  for (int p = 0; p < passes; p++) {
+    if (is_async(p + kPrefetch)) prefetch_tile(ring, (p + kPrefetch) % kScanRing, in, tile_of(p + kPrefetch));
+    asm volatile("cp.async.commit_group;" ::: "memory");
+
     // ---- fetch this tile into registers
-    if (is_async(tile)) {
-      asm volatile("cp.async.wait_group %0;" ::"n"(kScanRing - 1) : "memory");
-      const int slot = pass % kScanRing;
+    TileRegs<T> cur;
+    if (is_async(p)) {
+      asm volatile("cp.async.wait_group %0;" ::"n"(kPrefetch) : "memory");
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        const V t = *reinterpret_cast<const V *>(ring + (slot * 4 + j) * kScanThreads + threadIdx.x);
+        const V t = *reinterpret_cast<const V *>(slot_ptr(p, j));
         cur.v[j][0] = t.x, cur.v[j][1] = t.y, cur.v[j][2] = t.z, cur.v[j][3] = t.w;
       }
     } else {  // ragged last tile or unaligned pointers: guarded scalar loads
-      const long long base = tile_elem_base(tile);
+      const long long base = tile_elem_base(tile_of(p));
 #pragma unroll
       for (int j = 0; j < 4; j++)
 #pragma unroll
@@ -253,44 +317,29 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
       T excl = __shfl_up_sync(0xffffffffu, incl, 1);
       if (lane == 0) excl = 0;
       const T off = carry + excl;
-#pragma unroll
-      for (int c = 0; c < 4; c++) cur.v[j][c] += off;
+      V t;
+      t.x = cur.v[j][0] + off, t.y = cur.v[j][1] + off, t.z = cur.v[j][2] + off, t.w = cur.v[j][3] + off;
+      *reinterpret_cast<V *>(slot_ptr(p, j)) = t;  // park the warp-local scan in this thread's chunk
       carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    if (lane == 31) s_warp[par][warp] = carry;
-    __syncthreads();  // (A) warp totals of this pass visible; s_prefix of the previous pass consumed
+    if (lane == 31) s_warp[p & 1][warp] = carry;
+    named_bar_sync(BAR_TOTALS, kScanCtaThreads);  // warp totals visible to everybody, helper included
 
-    T warp_off = 0, block_total = 0;
 #pragma unroll
-    for (int w = 0; w < kScanThreads / 32; w++) {
-      const T t = s_warp[par][w];
-      if (w < warp) warp_off += t;
-      block_total += t;
-    }
+    for (int i = kStoreLag; i > 0; i--) woff[i] = woff[i - 1];
+    T warp_off = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; w++)
+      if (w < warp) warp_off += s_warp[p & 1][w];
+    woff[0] = warp_off;
 
-    if (warp == 0) {
-      // publish this tile's aggregate, then settle the PREVIOUS tile and start fetching for this one
-      if (lane == 0) st_state(state + tile, pack_state(to_bits<T>(block_total), epoch, ST_AGG));
-      if (have_prv) {
-        const T prefix = ((prv_tile < G) ? seed : running) + gather_finish<T>(pend, state, epoch);
-        if (lane == 0) s_prefix[par] = prefix;
-        running = prefix + prv_total;
-      }
-      gather_issue<T>(pend, state, tile, (tile < G) ? tile : G - 1);
-    }
-    __syncthreads();  // (B) prefix of the previous tile visible
-    if (have_prv) store_tile(prv, s_prefix[par] + prv_warp_off, out, n, prv_tile, vec_ok);
-    prv = cur, prv_warp_off = warp_off, prv_tile = tile, have_prv = true;
-    prv_total = block_total;
+    if (p >= kStoreLag) finish_tile(p - kStoreLag, woff[kStoreLag]);
   }
-  // epilogue: settle and store the last tile
-  if (have_prv) {
-    if (warp == 0) {
-      const T prefix = ((prv_tile < G) ? seed : running) + gather_finish<T>(pend, state, epoch);
-      if (lane == 0) s_prefix[0] = prefix;
-    }
-    __syncthreads();
-    store_tile(prv, s_prefix[0] + prv_warp_off, out, n, prv_tile, vec_ok);
+  // drain: the last kStoreLag tiles
+#pragma unroll
+  for (int d = kStoreLag; d > 0; d--) {
+    const int q = passes - d;
+    if (q >= 0) finish_tile(q, woff[d - 1]);
   }
 }
 
@@ -330,7 +379,7 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
   long long grid = (long long)ctx->sm_count * kScanCtasPerSM;  // all CTAs resident (see scan_kernel)
   if (grid > tiles) grid = tiles;
   CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
-  scan_kernel<T><<<(unsigned int)grid, kScanThreads, kScanSmemBytes, st>>>(in, out, n, seed, ctx->scan_state,
+  scan_kernel<T><<<(unsigned int)grid, kScanCtaThreads, kScanSmemBytes, st>>>(in, out, n, seed, ctx->scan_state,
                                                                ctx->scan_counter, ctx->scan_epoch,
                                                                (unsigned int)tiles);
   CUXB_LAUNCHED();
@@ -431,7 +480,7 @@ CUXB_API int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in,
   unsigned int grid = (unsigned int)d.sm_count * kScanCtasPerSM;  // every CTA resident at once
   if (grid > tiles) grid = tiles;
   CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<unsigned int>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
-  scan_kernel<unsigned int><<<grid, kScanThreads, kScanSmemBytes, st>>>((const unsigned int *)in, (unsigned int *)out, n,
+  scan_kernel<unsigned int><<<grid, kScanCtaThreads, kScanSmemBytes, st>>>((const unsigned int *)in, (unsigned int *)out, n,
                                                             (unsigned int)seed, d.scratch, counters, d.epoch, tiles);
   CUXB_LAUNCHED();
   return 0;
