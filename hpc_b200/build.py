@@ -31,7 +31,12 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=True):
+def build(force=False, verbose=True, extra_flags=(), out=None, build_dir=None):
+    """extra_flags / out / build_dir: build a variant library (tuning experiments) next to the default."""
+    global BUILD, SO
+    if out is not None:
+        BUILD, SO = build_dir or (out + ".build"), out
+        force = True
     os.makedirs(BUILD, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     headers.append(os.path.join(os.path.dirname(HERE), "include", "cuxb.h"))
@@ -42,7 +47,7 @@ def build(force=False, verbose=True):
         obj = os.path.join(BUILD, src[:-3] + ".o")
         objs.append(obj)
         if force or _stale(obj, [os.path.join(CSRC, src)] + headers):
-            jobs.append([NVCC] + FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj])
+            jobs.append([NVCC] + FLAGS + list(extra_flags) + ["-c", os.path.join(CSRC, src), "-o", obj])
 
     def run(cmd):
         if verbose:

@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcuxb.so")
+# CUXB_LIB_PATH selects a variant build of the same library (tuning experiments only)
+LIB_PATH = os.environ.get("CUXB_LIB_PATH") or os.path.join(_HERE, "libcuxb.so")
 
 FLOAT32, INT32, FLOAT16, INT8, BFLOAT16 = 0, 1, 2, 3, 4
 

@@ -181,8 +181,18 @@ constexpr int BAR_PREFIX = 2;                        // (+ pass % 4) the tile's 
 //   pass p + kGatherLag: the helper fetches the other CTAs' aggregates for tile p (published two
 //                        passes ago, so the loads come back ready) -> exclusive prefix of tile p
 //   pass p + kStoreLag : scan warps add the prefix and store tile p; its slot is free again
-constexpr int kPrefetch = 2, kGatherLag = 2, kStoreLag = 3;
-constexpr int kScanRing = 6;
+#ifndef CUXB_SCAN_PREFETCH
+#define CUXB_SCAN_PREFETCH 2
+#endif
+#ifndef CUXB_SCAN_GATHER_LAG
+#define CUXB_SCAN_GATHER_LAG 2
+#endif
+#ifndef CUXB_SCAN_STORE_LAG
+#define CUXB_SCAN_STORE_LAG 3
+#endif
+constexpr int kPrefetch = CUXB_SCAN_PREFETCH, kGatherLag = CUXB_SCAN_GATHER_LAG, kStoreLag = CUXB_SCAN_STORE_LAG;
+constexpr int kScanRing = kPrefetch + kStoreLag + 1;
+static_assert(kStoreLag > kGatherLag, "a tile's prefix must be settled before the pass that stores it");
 static_assert(kScanRing >= kPrefetch + kStoreLag + 1, "a slot must be stored before it is refilled");
 constexpr int kScanSmemBytes = kScanRing * kScanTileElems * 4;  // 192 KiB
 
@@ -202,7 +212,7 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
   extern __shared__ __align__(16) unsigned char scan_smem[];
   uint4 *ring = reinterpret_cast<uint4 *>(scan_smem);
   __shared__ T s_warp[2][kScanThreads / 32];
-  __shared__ T s_prefix[4];
+  __shared__ T s_add[4][kScanThreads / 32];  // per tile (mod 4) and scan warp: prefix + warp offset
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const bool vec_ok = ((((uintptr_t)in | (uintptr_t)out) & 15) == 0);
   const unsigned int G = gridDim.x;
@@ -212,37 +222,47 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
 
   if (warp == kScanThreads / 32) {
     // ===================================== helper warp =====================================
-    T running = 0;          // inclusive prefix of the last tile whose prefix was settled
-    T hist[kGatherLag + 1];  // block totals of the most recent passes, hist[0] = current
+    // Lane w < 16 keeps, for the last few passes, the exclusive offset of scan warp w inside its
+    // tile; all lanes keep the tile totals.  Settling tile q leaves  prefix(q) + offset(w)  for
+    // every scan warp in s_add[q & 3][w]: the scan warps need one shared-memory read per tile.
+    T running = 0;  // inclusive prefix of the last tile whose prefix was settled
+    T tot[kGatherLag + 1], off[kGatherLag + 1];
 #pragma unroll
-    for (int i = 0; i <= kGatherLag; i++) hist[i] = 0;
-    auto settle = [&](int q, T total_q) {
+    for (int i = 0; i <= kGatherLag; i++) tot[i] = 0, off[i] = 0;
+    auto settle = [&](int q, T total_q, T off_q) {
       const unsigned int tile = first_tile + (unsigned int)q * G;
       Gather<T> g;
       const bool first = tile < G;
       gather_issue<T>(g, state, tile, first ? tile : G - 1);
       const T prefix = (first ? seed : running) + gather_finish<T>(g, state, epoch);
       running = prefix + total_q;
-      if (lane == 0) s_prefix[q & 3] = prefix;
+      if (lane < kScanThreads / 32) s_add[q & 3][lane] = prefix + off_q;
       __threadfence_block();
       named_bar_arrive(BAR_PREFIX + (q & 3), kScanCtaThreads);
     };
     for (int p = 0; p < passes; p++) {
       named_bar_sync(BAR_TOTALS, kScanCtaThreads);
 #pragma unroll
-      for (int i = kGatherLag; i > 0; i--) hist[i] = hist[i - 1];
-      T total = 0;
+      for (int i = kGatherLag; i > 0; i--) tot[i] = tot[i - 1], off[i] = off[i - 1];
+      const T x = (lane < kScanThreads / 32) ? s_warp[p & 1][lane] : (T)0;
+      T incl = x;
 #pragma unroll
-      for (int w = 0; w < kScanThreads / 32; w++) total += s_warp[p & 1][w];
-      hist[0] = total;
-      if (lane == 0) st_state(state + first_tile + (unsigned int)p * G, pack_state(to_bits<T>(total), epoch, ST_AGG));
-      if (p >= kGatherLag) settle(p - kGatherLag, hist[kGatherLag]);
+      for (int o = 1; o < 32; o <<= 1) {
+        const T t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      T excl = __shfl_up_sync(0xffffffffu, incl, 1);
+      if (lane == 0) excl = 0;
+      tot[0] = __shfl_sync(0xffffffffu, incl, 31);
+      off[0] = excl;
+      if (lane == 0) st_state(state + first_tile + (unsigned int)p * G, pack_state(to_bits<T>(tot[0]), epoch, ST_AGG));
+      if (p >= kGatherLag) settle(p - kGatherLag, tot[kGatherLag], off[kGatherLag]);
     }
     // drain: the last kGatherLag tiles
 #pragma unroll
     for (int d = kGatherLag; d > 0; d--) {
       const int q = passes - d;
-      if (q >= 0) settle(q, hist[d - 1]);
+      if (q >= 0) settle(q, tot[d - 1], off[d - 1]);
     }
     return;
   }
@@ -252,33 +272,33 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
   auto is_async = [&](int q) {
     return vec_ok && q < passes && (long long)(tile_of(q) + 1) * kScanTileElems <= n;
   };
-  auto slot_ptr = [&](int q, int j) { return ring + ((q % kScanRing) * 4 + j) * kScanThreads + threadIdx.x; };
+  auto slot_ptr = [&](int slot, int j) { return ring + (slot * 4 + j) * kScanThreads + threadIdx.x; };
   // add the settled prefix to a parked tile and write it out
-  auto finish_tile = [&](int q, T warp_off_q) {
+  auto finish_tile = [&](int q, int slot) {
     named_bar_sync(BAR_PREFIX + (q & 3), kScanCtaThreads);
-    const T add = s_prefix[q & 3] + warp_off_q;
+    const T add = s_add[q & 3][warp];
     TileRegs<T> r;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      const V t = *reinterpret_cast<const V *>(slot_ptr(q, j));
+      const V t = *reinterpret_cast<const V *>(slot_ptr(slot, j));
       r.v[j][0] = t.x, r.v[j][1] = t.y, r.v[j][2] = t.z, r.v[j][3] = t.w;
     }
     store_tile(r, add, out, n, tile_of(q), vec_ok);
   };
+  auto next_slot = [](int s) { return s + 1 == kScanRing ? 0 : s + 1; };
 
   // prologue: start the first kPrefetch tiles (one commit group per pass, even when empty, so
   // that wait_group counts passes)
 #pragma unroll
   for (int d = 0; d < kPrefetch; d++) {
-    if (is_async(d)) prefetch_tile(ring, d % kScanRing, in, tile_of(d));
+    if (is_async(d)) prefetch_tile(ring, d, in, tile_of(d));
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
 
-  T woff[kStoreLag + 1];  // warp offsets of the tiles still parked in the ring, woff[0] = current
-#pragma unroll
-  for (int i = 0; i <= kStoreLag; i++) woff[i] = 0;
+  // ring positions: tile p sits in slot p % kScanRing (kept as counters -- no division in the loop)
+  int slot_cur = 0, slot_pf = kPrefetch % kScanRing, slot_st = (kScanRing - kStoreLag) % kScanRing;
   for (int p = 0; p < passes; p++) {
-    if (is_async(p + kPrefetch)) prefetch_tile(ring, (p + kPrefetch) % kScanRing, in, tile_of(p + kPrefetch));
+    if (is_async(p + kPrefetch)) prefetch_tile(ring, slot_pf, in, tile_of(p + kPrefetch));
     asm volatile("cp.async.commit_group;" ::: "memory");
 
     // ---- fetch this tile into registers
@@ -287,7 +307,7 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
       asm volatile("cp.async.wait_group %0;" ::"n"(kPrefetch) : "memory");
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        const V t = *reinterpret_cast<const V *>(slot_ptr(p, j));
+        const V t = *reinterpret_cast<const V *>(slot_ptr(slot_cur, j));
         cur.v[j][0] = t.x, cur.v[j][1] = t.y, cur.v[j][2] = t.z, cur.v[j][3] = t.w;
       }
     } else {  // ragged last tile or unaligned pointers: guarded scalar loads
@@ -319,27 +339,20 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
       const T off = carry + excl;
       V t;
       t.x = cur.v[j][0] + off, t.y = cur.v[j][1] + off, t.z = cur.v[j][2] + off, t.w = cur.v[j][3] + off;
-      *reinterpret_cast<V *>(slot_ptr(p, j)) = t;  // park the warp-local scan in this thread's chunk
+      *reinterpret_cast<V *>(slot_ptr(slot_cur, j)) = t;  // park the warp-local scan in this thread's chunk
       carry += __shfl_sync(0xffffffffu, incl, 31);
     }
     if (lane == 31) s_warp[p & 1][warp] = carry;
-    named_bar_sync(BAR_TOTALS, kScanCtaThreads);  // warp totals visible to everybody, helper included
+    named_bar_sync(BAR_TOTALS, kScanCtaThreads);  // warp totals handed to the helper warp
 
-#pragma unroll
-    for (int i = kStoreLag; i > 0; i--) woff[i] = woff[i - 1];
-    T warp_off = 0;
-#pragma unroll
-    for (int w = 0; w < kScanThreads / 32; w++)
-      if (w < warp) warp_off += s_warp[p & 1][w];
-    woff[0] = warp_off;
-
-    if (p >= kStoreLag) finish_tile(p - kStoreLag, woff[kStoreLag]);
+    if (p >= kStoreLag) finish_tile(p - kStoreLag, slot_st);
+    slot_cur = next_slot(slot_cur), slot_pf = next_slot(slot_pf), slot_st = next_slot(slot_st);
   }
   // drain: the last kStoreLag tiles
 #pragma unroll
   for (int d = kStoreLag; d > 0; d--) {
     const int q = passes - d;
-    if (q >= 0) finish_tile(q, woff[d - 1]);
+    if (q >= 0) finish_tile(q, q % kScanRing);
   }
 }
 
