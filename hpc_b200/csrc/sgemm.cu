@@ -119,25 +119,30 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
     if (FAST) asm volatile("cp.async.wait_group 0;" ::: "memory");
   };
 
-  float acc[8][8];
+  // Accumulators are kept as row PAIRS so the inner product runs on packed FFMA2 (fma.rn.f32x2,
+  // sm_100): acc2[ip][j] = (C[2ip][j], C[2ip+1][j]).  FFMA2 has the same FLOP rate as FFMA but
+  // needs half the issue slots (measured, tools/fp32_peak.cu), which is what a 4-LDS-per-64-FMA
+  // loop is short of.  Each lane is an ordinary IEEE fp32 fma, so results are unchanged.
+  float2 acc2[4][8];
 #pragma unroll
-  for (int i = 0; i < 8; i++)
+  for (int i = 0; i < 4; i++)
 #pragma unroll
-    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+    for (int j = 0; j < 8; j++) acc2[i][j] = make_float2(0.f, 0.f);
 
   const int KT = (p.K + SG_BK - 1) / SG_BK;
   gload(0, 0);
   sstore(0);
   __syncthreads();
 
-  float af[2][8], bf[2][8];
+  float2 af[2][4];  // (a0,a1) (a2,a3) (a4,a5) (a6,a7)
+  float bf[2][8];
   auto lfrag = [&](int buf, int k, int s) {
     const float4 a0 = *reinterpret_cast<const float4 *>(&As[buf][k][tm0]);
     const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][k][tm0 + 32]);
     const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[buf][k][tn0]);
     const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[buf][k][tn0 + 16]);
-    af[s][0] = a0.x, af[s][1] = a0.y, af[s][2] = a0.z, af[s][3] = a0.w;
-    af[s][4] = a1.x, af[s][5] = a1.y, af[s][6] = a1.z, af[s][7] = a1.w;
+    af[s][0] = make_float2(a0.x, a0.y), af[s][1] = make_float2(a0.z, a0.w);
+    af[s][2] = make_float2(a1.x, a1.y), af[s][3] = make_float2(a1.z, a1.w);
     bf[s][0] = b0.x, bf[s][1] = b0.y, bf[s][2] = b0.z, bf[s][3] = b0.w;
     bf[s][4] = b1.x, bf[s][5] = b1.y, bf[s][6] = b1.z, bf[s][7] = b1.w;
   };
@@ -151,13 +156,21 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
     for (int k = 0; k < SG_BK; k++) {
       if (k + 1 < SG_BK) lfrag(buf, k + 1, (k + 1) & 1);
 #pragma unroll
-      for (int i = 0; i < 8; i++)
+      for (int j = 0; j < 8; j++) {
+        const float2 bb = make_float2(bf[k & 1][j], bf[k & 1][j]);
 #pragma unroll
-        for (int j = 0; j < 8; j++) acc[i][j] = fmaf(af[k & 1][i], bf[k & 1][j], acc[i][j]);
+        for (int ip = 0; ip < 4; ip++) acc2[ip][j] = __ffma2_rn(af[k & 1][ip], bb, acc2[ip][j]);
+      }
     }
     if (more) sstore(buf ^ 1);
     __syncthreads();
   }
+
+  float acc[8][8];
+#pragma unroll
+  for (int ip = 0; ip < 4; ip++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[2 * ip][j] = acc2[ip][j].x, acc[2 * ip + 1][j] = acc2[ip][j].y;
 
   // epilogue
 #pragma unroll
