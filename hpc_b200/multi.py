@@ -1,0 +1,62 @@
+"""Host-side logic of the multi-GPU paths (one process per GPU, torch.distributed).
+
+Only what the hot path needs (north_star):
+  * reductions: a per-GPU partial, then ONE all-reduce of the scalar            -> allreduce_sum / nrm2_combine
+  * int32 scan: per-GPU totals exchanged, every rank seeds its local scan with
+    the sum of the lower ranks' totals (what MPI_Exscan does in the reference's
+    mpi/base_reduce_alltoall_scan.cpp:101)                                       -> scan_seed
+  * GEMM / linear: rows of A and C sharded, B replicated (the decomposition of
+    mpi/alg_matrix_multiply.cpp:52-67); no collective on the data path           -> shard_rows
+The functions take tensors on whatever device the process group's backend serves (cuda for nccl,
+cpu for gloo), so the same code is exercised by the world_size-2 gloo tests on CPU.
+"""
+import torch
+
+
+def shard_range(n, world, rank):
+    """Contiguous slice [lo, hi) of n items owned by `rank`; the first n % world ranks get one more."""
+    base, rem = divmod(n, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_rows(M, world, rank):
+    return shard_range(M, world, rank)
+
+
+def allreduce_sum(dist, partial):
+    """One all-reduce of the per-GPU partial (in place).  Sum order across ranks is NCCL's; with the
+    reference's integer-valued fills it is exact in any order."""
+    if dist is not None and dist.get_world_size() > 1:
+        dist.all_reduce(partial)
+    return partial
+
+
+def nrm2_combine(dist, local_norm, scratch=None):
+    """Combine per-GPU Euclidean norms: sqrt(sum_r norm_r^2)."""
+    if dist is None or dist.get_world_size() == 1:
+        return local_norm
+    sq = scratch if scratch is not None else torch.empty_like(local_norm)
+    torch.mul(local_norm, local_norm, out=sq)
+    dist.all_reduce(sq)
+    torch.sqrt(sq, out=local_norm)
+    return local_norm
+
+
+def wrap_i32(v):
+    """Python int -> the int32 it wraps to (two's complement)."""
+    return (int(v) + 2 ** 31) % 2 ** 32 - 2 ** 31
+
+
+def scan_seed(dist, local_total, gathered=None):
+    """Exclusive prefix over ranks of the per-GPU int32 totals, with int32 wrap-around.
+    local_total: 1-element int32 tensor.  Returns a Python int to pass as `seed`."""
+    if dist is None or dist.get_world_size() == 1:
+        return 0
+    world, rank = dist.get_world_size(), dist.get_rank()
+    if gathered is None:
+        gathered = torch.empty(world, dtype=torch.int32, device=local_total.device)
+    dist.all_gather_into_tensor(gathered, local_total)
+    if rank == 0:
+        return 0
+    return wrap_i32(int(gathered[:rank].to(torch.int64).sum().item()))
