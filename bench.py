@@ -341,6 +341,9 @@ def main():
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
+        # keep stdout to the single JSON line: NCCL's version banner (NCCL_DEBUG=VERSION) goes there
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", ""):
+            os.environ["NCCL_DEBUG"] = "WARN"
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = capi.Context(local)
