@@ -113,9 +113,10 @@ class Workload:
         return self.torch.randint(lo, hi + 1, shape, device="cuda", generator=g, dtype=self.torch.int32).to(dtype)
 
 
-def make_workload(name, torch, ctx, world, rank, dist):
+def make_workload(name, torch, ctx, world, rank, dist, peers=None):
     from hpc_b200 import capi, multi
     W = Workload(torch, ctx, world)
+    W.collective = "none"
     stream = lambda: torch.cuda.current_stream().cuda_stream
     seed = 20240607 + 17 * rank
     if name in ("dot", "sum", "nrm2"):
@@ -128,13 +129,22 @@ def make_workload(name, torch, ctx, world, rank, dist):
               "nrm2": lambda: ctx.nrm2_f32(n, a.data_ptr(), res.data_ptr(), stream())}[name]
         sq = torch.zeros(1, device="cuda")
 
-        def step():
+        def step_nccl():
             fn()                                   # per-GPU partial (one kernel launch)
             if world > 1:                          # then ONE NCCL all-reduce of the scalar
                 if name == "nrm2":
                     multi.nrm2_combine(dist, res, sq)
                 else:
                     multi.allreduce_sum(dist, res)
+        step = step_nccl
+        W.collective = "none (1 GPU)" if world == 1 else "nccl all-reduce of the scalar after the kernel"
+        W.step_nccl = step_nccl
+        if world > 1 and peers is not None:
+            mg = {"dot": lambda: ctx.mg_dot_f32(n, a.data_ptr(), b.data_ptr(), res.data_ptr(), world, rank, peers.ptrs, stream()),
+                  "sum": lambda: ctx.mg_sum_f32(n, a.data_ptr(), res.data_ptr(), world, rank, peers.ptrs, stream()),
+                  "nrm2": lambda: ctx.mg_nrm2_f32(n, a.data_ptr(), res.data_ptr(), world, rank, peers.ptrs, stream())}[name]
+            step = mg
+            W.collective = "fused: partials exchanged over NVLink peer memory inside the reduction kernel (no NCCL launch)"
         W.kernel = fn
         W.step = step
         W.units = (8 if name == "dot" else 4) * n
@@ -164,6 +174,11 @@ def make_workload(name, torch, ctx, world, rank, dist):
                 seed_val = multi.scan_seed(dist, tot, gathered)
                 ctx.scan_i32(n, x.data_ptr(), out.data_ptr(), seed_val, stream())
             W.launches_per_step = 2
+            W.collective = "nccl all-gather of per-GPU totals + host-computed seed"
+            W.step_nccl = step
+            if peers is not None:
+                step = lambda: ctx.mg_scan_i32(n, x.data_ptr(), out.data_ptr(), world, rank, peers.ptrs, stream())
+                W.collective = "fused: totals exchanged over NVLink peer memory inside the reduction kernel; seed read from device memory (no host sync, no NCCL launch)"
         W.kernel, W.step = fn, step
         W.units = 8 * n
         W.unit, W.bound, W.dtype = "GB/s", "hbm", "i32"
@@ -325,6 +340,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", default="dot", choices=["dot", "sum", "nrm2", "scan", "sgemm", "hgemm", "linear_s8"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
+                    help="N>1: exchange fused into the kernel over peer memory (default) or a NCCL collective after it")
     ap.add_argument("--no-also", action="store_true", help="skip the short passes over the other workloads")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     args = ap.parse_args()
@@ -348,7 +365,14 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = capi.Context(local)
     peaks = load_peaks()
-    W = make_workload(args.workload, torch, ctx, world, rank, dist)
+    peers, peers_note = None, None
+    if world > 1 and args.collective == "fused":
+        try:
+            from hpc_b200 import multi
+            peers = multi.PeerExchange(dist, torch.device("cuda", local))
+        except Exception as ex:  # reported in the JSON line, never silent
+            peers_note = "peer-memory rendezvous failed (%s): NCCL collective used instead" % str(ex)[:200]
+    W = make_workload(args.workload, torch, ctx, world, rank, dist, peers)
     warmup = max(args.warmup, 3)
 
     # ---- device-resident timing (value)
@@ -361,6 +385,13 @@ def main():
     launches = (capi.launch_count() - l0) - warmup * W.launches_per_step
     ms_step = ms_total / args.steps
     value = rate(W.units * world, ms_step, W.unit)
+    collective_desc = W.collective if peers_note is None else peers_note
+
+    nccl_variant = None
+    if world > 1 and peers is not None and hasattr(W, "step_nccl"):
+        ms_n, _, _ = time_steps(torch, W.step_nccl, args.steps, 3, dist)
+        nccl_variant = {"ms_per_step": ms_n / args.steps, "value": rate(W.units * world, ms_n / args.steps, W.unit),
+                        "what": "same kernel followed by a NCCL collective on the scalar(s)"}
 
     # ---- the dominant kernel alone, on the launching stream (roofline.achieved)
     ms_k, _, t1k = time_steps(torch, W.kernel, args.steps, 3, None)
@@ -462,7 +493,7 @@ def main():
                        "GEMM operands exceed L2; no flush", "parallelism": "one rank per GPU, per-GPU partial + one NCCL all-reduce"
                        if wl["hbm"] else "rows of C sharded per GPU, B replicated"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "also": also,
+            "collective": collective_desc, "nccl_variant": nccl_variant, "also": also,
         }
         print(json.dumps(line))
     if dist is not None:

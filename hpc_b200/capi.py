@@ -58,6 +58,12 @@ SIGNATURES = {
     "cuxb_scan_i32": ([_vp, _vp, _ll, _vp, _vp, C.c_int32], _i),
     "cuxb_scan_f32": ([_vp, _vp, _ll, _vp, _vp, _f], _i),
     "cuxb_scan_i32_noalloc": ([_vp, _ll, _vp, _vp, C.c_int32], _i),
+    "cuxb_mg_dot_f32": ([_vp, _vp, _ll, _vp, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
+    "cuxb_mg_sum_f32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
+    "cuxb_mg_nrm2_f32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
+    "cuxb_mg_exscan_total_i32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
+    "cuxb_mg_scan_i32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
+    "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
     "cuxb_linear_s8_s32": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp], _i),
@@ -169,6 +175,23 @@ class Context:
     def linear_f16(self, M, N, K, A, Bt, Cp, c_dtype=FLOAT16, stream=0):
         check(lib().cuxb_linear_f16_f32acc(self._h, stream, M, N, K, A, Bt, Cp, c_dtype),
               "cuxb_linear_f16_f32acc")
+
+    # --- multi-GPU: reductions / scan with the scalar exchange fused into the kernel (peer memory) ---
+    @staticmethod
+    def _peers(ptrs):
+        return (_vp * len(ptrs))(*ptrs)
+
+    def mg_dot_f32(self, n, a, b, res, world, rank, peer_ptrs, stream=0):
+        check(lib().cuxb_mg_dot_f32(self._h, stream, n, a, b, res, world, rank, self._peers(peer_ptrs)), "cuxb_mg_dot_f32")
+
+    def mg_sum_f32(self, n, x, res, world, rank, peer_ptrs, stream=0):
+        check(lib().cuxb_mg_sum_f32(self._h, stream, n, x, res, world, rank, self._peers(peer_ptrs)), "cuxb_mg_sum_f32")
+
+    def mg_nrm2_f32(self, n, x, res, world, rank, peer_ptrs, stream=0):
+        check(lib().cuxb_mg_nrm2_f32(self._h, stream, n, x, res, world, rank, self._peers(peer_ptrs)), "cuxb_mg_nrm2_f32")
+
+    def mg_scan_i32(self, n, src, dst, world, rank, peer_ptrs, stream=0):
+        check(lib().cuxb_mg_scan_i32(self._h, stream, n, src, dst, world, rank, self._peers(peer_ptrs)), "cuxb_mg_scan_i32")
 
     def convert(self, n, src, src_dtype, dst, dst_dtype, stream=0):
         check(lib().cuxb_convert(self._h, stream, n, src, src_dtype, dst, dst_dtype), "cuxb_convert")

@@ -73,6 +73,8 @@ struct cuxb_ctx {
   unsigned int *scan_counter;  // [0] tile ticket, [1] finished tiles
   long long scan_state_tiles;
   unsigned int scan_epoch;
+  unsigned int mg_epoch;       // multi-GPU exchange epoch (all ranks make the same sequence of mg calls)
+  int *mg_seed;                // device int32: the sharded scan's exclusive offset
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];

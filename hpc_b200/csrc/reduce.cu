@@ -42,6 +42,69 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
   return r;
 }
 
+// ---- multi-GPU: the scalar exchange is part of the reduction kernel.  Every rank's finishing CTA
+// writes its partial (value | epoch in one 64-bit word) straight into EVERY rank's exchange buffer
+// over NVLink (peer-mapped pointers), then waits until its own buffer holds this call's word from
+// every rank and adds them up in rank order -- so all ranks get the same, order-fixed result without
+// a separate collective launch.  Slots alternate with the epoch's parity: a rank that runs one call
+// ahead writes the other half, and it cannot run two ahead because it needs everybody's word first.
+struct MgExchange {
+  int world, rank;              // world <= 1: single GPU, no exchange
+  unsigned int epoch;           // identical on every rank for this call, never 0
+  int mode;                     // 0: sum over all ranks   1: exclusive prefix (sum of the lower ranks)
+  unsigned long long *peer[8];  // peer[r] = rank r's exchange buffer (>= CUXB_MG_EXCHANGE_BYTES)
+};
+__device__ __forceinline__ void st_sys_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_sys_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+template <typename T> __device__ __forceinline__ unsigned int bits_of(T v);
+template <> __device__ __forceinline__ unsigned int bits_of<float>(float v) { return __float_as_uint(v); }
+template <> __device__ __forceinline__ unsigned int bits_of<unsigned int>(unsigned int v) { return v; }
+template <typename T> __device__ __forceinline__ T of_bits(unsigned int v);
+template <> __device__ __forceinline__ float of_bits<float>(unsigned int v) { return __uint_as_float(v); }
+template <> __device__ __forceinline__ unsigned int of_bits<unsigned int>(unsigned int v) { return v; }
+
+// Executed by warp 0 of the finishing CTA.  Returns the combined value to every lane.
+template <typename T>
+__device__ __forceinline__ T mg_exchange(const MgExchange &mg, T mine) {
+  const int lane = threadIdx.x & 31;
+  const int slot = (mg.epoch & 1) * 8;
+  const unsigned long long word = ((unsigned long long)bits_of<T>(mine) << 32) | mg.epoch;
+  unsigned long long *dst = nullptr, *own = nullptr;
+#pragma unroll
+  for (int r = 0; r < 8; r++) {
+    if (r == lane) dst = mg.peer[r];
+    if (r == mg.rank) own = mg.peer[r];
+  }
+  if (lane < mg.world) st_sys_u64(dst + slot + mg.rank, word);
+  unsigned long long w = 0;
+  if (lane < mg.world) {
+    const unsigned long long t0 = global_timer_ns();
+    while (true) {
+      w = ld_sys_u64(own + slot + lane);
+      if ((unsigned int)w == mg.epoch) break;
+      if (global_timer_ns() - t0 > 20000000000ull) __trap();  // a rank never arrived: fail, do not hang
+    }
+  }
+  const T val = (lane < mg.world) ? of_bits<T>((unsigned int)(w >> 32)) : (T)0;
+  T total = 0;
+  for (int r = 0; r < mg.world; r++) {  // rank order: every rank adds in the same order
+    const T vr = __shfl_sync(0xffffffffu, val, r);
+    if (mg.mode == 0 || r < mg.rank) total += vr;
+  }
+  return total;
+}
+
 template <typename T> struct Vec4;
 template <> struct Vec4<float> { typedef float4 type; };
 template <> struct Vec4<unsigned int> { typedef uint4 type; };
@@ -88,7 +151,7 @@ template <int OP, typename T, int VEC>
 __global__ void __launch_bounds__(kRedThreads, kRedBlocksPerSM)
 reduce_kernel(const T *__restrict__ a, const T *__restrict__ b, long long n,
               T *__restrict__ partials, unsigned int *__restrict__ ticket, T *__restrict__ res,
-              int finish_sqrt) {
+              int finish_sqrt, const MgExchange mg) {
   __shared__ T smem[kRedThreads / 32];
   __shared__ bool is_last;
   typedef typename Vec4<T>::type V;
@@ -142,10 +205,11 @@ reduce_kernel(const T *__restrict__ a, const T *__restrict__ b, long long n,
   T p = 0;
   for (int i = threadIdx.x; i < (int)gridDim.x; i += kRedThreads) p += __ldcg(partials + i);
   p = block_sum(p, smem);
+  if (mg.world > 1 && threadIdx.x < 32) p = mg_exchange<T>(mg, p);  // warp 0 holds the CTA total
   if (threadIdx.x == 0) {
     if (finish_sqrt) {
-      // Nrm2HostV0 (nrm2.cpp:8-9): n == 1 -> |x0| exactly
-      float f = (n == 1) ? fabsf((float)a[0]) : sqrtf((float)p);
+      // Nrm2HostV0 (nrm2.cpp:8-9): n == 1 -> |x0| exactly (single GPU)
+      float f = (n == 1 && mg.world <= 1) ? fabsf((float)a[0]) : sqrtf((float)p);
       res[0] = (T)f;
     } else {
       res[0] = p;
@@ -165,33 +229,37 @@ static int reduce_grid(const cuxb_ctx *ctx, long long n) {
 
 template <int OP, typename T>
 static int launch_reduce(cuxb_ctx *ctx, cudaStream_t st, long long n, const T *a, const T *b, T *res,
-                         int finish_sqrt, void *partials, unsigned int *ticket, int grid_cap) {
+                         int finish_sqrt, void *partials, unsigned int *ticket, int grid_cap,
+                         const MgExchange &mg) {
   const int grid = grid_cap;
   const bool aligned = (((uintptr_t)a | (uintptr_t)(OP == OP_DOT ? b : a)) & 15) == 0;
   if (aligned)
-    reduce_kernel<OP, T, 4><<<grid, kRedThreads, 0, st>>>(a, b, n, (T *)partials, ticket, res, finish_sqrt);
+    reduce_kernel<OP, T, 4><<<grid, kRedThreads, 0, st>>>(a, b, n, (T *)partials, ticket, res, finish_sqrt, mg);
   else
-    reduce_kernel<OP, T, 1><<<grid, kRedThreads, 0, st>>>(a, b, n, (T *)partials, ticket, res, finish_sqrt);
+    reduce_kernel<OP, T, 1><<<grid, kRedThreads, 0, st>>>(a, b, n, (T *)partials, ticket, res, finish_sqrt, mg);
   CUXB_LAUNCHED();
   return 0;
 }
 
 template <int OP, typename T>
 static int reduce_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n, const T *a,
-                        const T *b, T *res, int finish_sqrt) {
+                        const T *b, T *res, int finish_sqrt, const MgExchange *mgp = nullptr) {
+  MgExchange mg;
+  memset(&mg, 0, sizeof(mg));
+  if (mgp) mg = *mgp;
   int rc = ensure_device(ctx);
   if (rc) return rc;
   CUXB_REQUIRE(res != nullptr, CUXB_ERR_INVALID, "%s: result pointer is null", name);
   CUXB_REQUIRE(n >= 0, CUXB_ERR_INVALID, "%s: negative length %lld", name, n);
   cudaStream_t st = (cudaStream_t)stream;
-  if (n == 0) {
+  if (n == 0 && mg.world <= 1) {
     CUXB_CUDA(cudaMemsetAsync(res, 0, sizeof(T), st));
     return 0;
   }
-  CUXB_REQUIRE(a != nullptr && (OP != OP_DOT || b != nullptr), CUXB_ERR_INVALID,
+  CUXB_REQUIRE(n == 0 || (a != nullptr && (OP != OP_DOT || b != nullptr)), CUXB_ERR_INVALID,
                "%s: input pointer is null", name);
   return launch_reduce<OP, T>(ctx, st, n, a, b, res, finish_sqrt, ctx->red_partials,
-                              ctx->red_ticket, reduce_grid(ctx, n));
+                              ctx->red_ticket, reduce_grid(ctx, n), mg);
 }
 
 const void *reduce_kernel_symbol(const char *name) {
@@ -218,4 +286,62 @@ CUXB_API int cuxb_nrm2_f32(cuxb_ctx *ctx, void *stream, long long n, const float
 CUXB_API int cuxb_sum_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *x, int32_t *res) {
   return reduce_entry<OP_SUM, unsigned int>("cuxb_sum_i32", ctx, stream, n, (const unsigned int *)x,
                                             nullptr, (unsigned int *)res, 0);
+}
+
+// ---- multi-GPU entry points: the same kernels with the scalar exchange fused into the finishing CTA
+namespace cuxb {
+int mg_prepare(const char *name, cuxb_ctx *ctx, int world, int rank, void *const *peer_bufs, int mode, MgExchange *mg) {
+  CUXB_REQUIRE(ctx != nullptr, CUXB_ERR_INVALID, "%s: null ctx", name);
+  CUXB_REQUIRE(world >= 1 && world <= 8 && rank >= 0 && rank < world, CUXB_ERR_INVALID,
+               "%s: world=%d rank=%d (1..8 ranks supported)", name, world, rank);
+  memset(mg, 0, sizeof(*mg));
+  mg->world = world, mg->rank = rank, mg->mode = mode;
+  if (world == 1) return 0;
+  CUXB_REQUIRE(peer_bufs != nullptr, CUXB_ERR_INVALID, "%s: peer_bufs is null", name);
+  for (int r = 0; r < world; r++) {
+    CUXB_REQUIRE(peer_bufs[r] != nullptr && ((uintptr_t)peer_bufs[r] & 7) == 0, CUXB_ERR_INVALID,
+                 "%s: peer buffer %d is null or not 8-byte aligned", name, r);
+    mg->peer[r] = (unsigned long long *)peer_bufs[r];
+  }
+  ctx->mg_epoch = ctx->mg_epoch + 1;
+  if (ctx->mg_epoch == 0) ctx->mg_epoch = 1;
+  mg->epoch = ctx->mg_epoch;
+  return 0;
+}
+}  // namespace cuxb
+
+CUXB_API int cuxb_mg_dot_f32(cuxb_ctx *ctx, void *stream, long long n, const float *a, const float *b, float *res,
+                             int world, int rank, void *const *peer_bufs) {
+  MgExchange mg;
+  int rc = mg_prepare("cuxb_mg_dot_f32", ctx, world, rank, peer_bufs, 0, &mg);
+  if (rc) return rc;
+  return reduce_entry<OP_DOT, float>("cuxb_mg_dot_f32", ctx, stream, n, a, b, res, 0, &mg);
+}
+CUXB_API int cuxb_mg_sum_f32(cuxb_ctx *ctx, void *stream, long long n, const float *x, float *res, int world,
+                             int rank, void *const *peer_bufs) {
+  MgExchange mg;
+  int rc = mg_prepare("cuxb_mg_sum_f32", ctx, world, rank, peer_bufs, 0, &mg);
+  if (rc) return rc;
+  return reduce_entry<OP_SUM, float>("cuxb_mg_sum_f32", ctx, stream, n, x, nullptr, res, 0, &mg);
+}
+CUXB_API int cuxb_mg_nrm2_f32(cuxb_ctx *ctx, void *stream, long long n, const float *x, float *res, int world,
+                              int rank, void *const *peer_bufs) {
+  MgExchange mg;
+  int rc = mg_prepare("cuxb_mg_nrm2_f32", ctx, world, rank, peer_bufs, 0, &mg);
+  if (rc) return rc;
+  return reduce_entry<OP_SUMSQ, float>("cuxb_mg_nrm2_f32", ctx, stream, n, x, nullptr, res, 1, &mg);
+}
+// exclusive prefix over ranks of the per-GPU int32 totals -> *seed_out (device): phase 1 of the sharded scan
+CUXB_API int cuxb_mg_exscan_total_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *x, int32_t *seed_out,
+                                      int world, int rank, void *const *peer_bufs) {
+  MgExchange mg;
+  int rc = mg_prepare("cuxb_mg_exscan_total_i32", ctx, world, rank, peer_bufs, 1, &mg);
+  if (rc) return rc;
+  if (world == 1) {  // nothing in front of the only rank
+    CUXB_REQUIRE(seed_out != nullptr, CUXB_ERR_INVALID, "cuxb_mg_exscan_total_i32: null seed_out");
+    CUXB_CUDA(cudaMemsetAsync(seed_out, 0, 4, (cudaStream_t)stream));
+    return 0;
+  }
+  return reduce_entry<OP_SUM, unsigned int>("cuxb_mg_exscan_total_i32", ctx, stream, n, (const unsigned int *)x, nullptr,
+                                            (unsigned int *)seed_out, 0, &mg);
 }

@@ -82,6 +82,8 @@ CUXB_API int cuxb_ctx_create(int device, cuxb_ctx **out) {
     return (int)e;
   }
   c->scan_epoch = 0;
+  c->mg_epoch = 0;
+  c->mg_seed = (int *)((char *)c->red_ticket + 128);  // inside the zeroed 256-byte block
   *out = c;
   return 0;
 }
@@ -180,6 +182,20 @@ CUXB_API int cuxb_device_info(int device, int *sm_count, int *cc_major, int *cc_
   if (warp_size) *warp_size = prop.warpSize;
   if (global_mem_bytes) *global_mem_bytes = prop.totalGlobalMem;
   if (shared_mem_per_block) *shared_mem_per_block = prop.sharedMemPerBlock;
+  return 0;
+}
+
+CUXB_API int cuxb_enable_peer_access(int device, int peer_device) {
+  int can = 0;
+  CUXB_CUDA(cudaDeviceCanAccessPeer(&can, device, peer_device));
+  CUXB_REQUIRE(can, CUXB_ERR_UNSUPPORTED, "device %d cannot access device %d directly", device, peer_device);
+  int cur = -1;
+  CUXB_CUDA(cudaGetDevice(&cur));
+  CUXB_CUDA(cudaSetDevice(device));
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+  cudaSetDevice(cur);
+  CUXB_CUDA(e);
   return 0;
 }
 

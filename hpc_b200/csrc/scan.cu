@@ -202,12 +202,11 @@ constexpr int kScanSmemBytes = kScanRing * kScanTileElems * 4;  // 192 KiB
 //     its own cp.async, so cp.async.wait_group is all the synchronisation the data needs).
 //   * 1 helper warp: aggregate publication and prefix gathering; its L2 round trips never sit on
 //     the scan warps' critical path.
-// `counter` is unused (kept for the callers' scratch layout).
 template <typename T>
 __global__ void __launch_bounds__(kScanCtaThreads, 1)
-scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__restrict__ state,
-            unsigned int *__restrict__ counter, unsigned int epoch, unsigned int num_tiles) {
-  (void)counter;
+scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed_ptr,
+            unsigned long long *__restrict__ state, unsigned int epoch, unsigned int num_tiles) {
+  if (seed_ptr != nullptr) seed += *seed_ptr;  // sharded scan: the exclusive offset computed on the device
   typedef typename V4<T>::type V;
   extern __shared__ __align__(16) unsigned char scan_smem[];
   uint4 *ring = reinterpret_cast<uint4 *>(scan_smem);
@@ -358,7 +357,7 @@ scan_kernel(const T *in, T *out, long long n, T seed, unsigned long long *__rest
 
 template <typename T>
 static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n, const T *in, T *out,
-                      T seed) {
+                      T seed, const T *seed_ptr = nullptr) {
   int rc = ensure_device(ctx);
   if (rc) return rc;
   CUXB_REQUIRE(n >= 0, CUXB_ERR_INVALID, "%s: negative length %lld", name, n);
@@ -392,9 +391,8 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
   long long grid = (long long)ctx->sm_count * kScanCtasPerSM;  // all CTAs resident (see scan_kernel)
   if (grid > tiles) grid = tiles;
   CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
-  scan_kernel<T><<<(unsigned int)grid, kScanCtaThreads, kScanSmemBytes, st>>>(in, out, n, seed, ctx->scan_state,
-                                                               ctx->scan_counter, ctx->scan_epoch,
-                                                               (unsigned int)tiles);
+  scan_kernel<T><<<(unsigned int)grid, kScanCtaThreads, kScanSmemBytes, st>>>(in, out, n, seed, seed_ptr, ctx->scan_state,
+                                                               ctx->scan_epoch, (unsigned int)tiles);
   CUXB_LAUNCHED();
   return 0;
 }
@@ -483,7 +481,6 @@ CUXB_API int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in,
   // every state word carries the epoch of the launch that wrote it, this launch gets a fresh epoch,
   // and a word with any other epoch reads as "not published yet".  Only when the 30-bit epoch wraps
   // are the words wiped (on the caller's stream, ahead of the kernel).
-  unsigned int *counters = reinterpret_cast<unsigned int *>(d.scratch + kNoAllocMaxTiles);  // reserved, unused
   d.epoch = (d.epoch + 1) & 0x3fffffffu;
   if (d.epoch == 0) {  // epoch wrapped after 2^30 calls: wipe the state words once and skip 0
     CUXB_CUDA(cudaMemsetAsync(d.scratch, 0, (size_t)kNoAllocMaxTiles * sizeof(unsigned long long), st));
@@ -494,7 +491,23 @@ CUXB_API int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in,
   if (grid > tiles) grid = tiles;
   CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<unsigned int>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
   scan_kernel<unsigned int><<<grid, kScanCtaThreads, kScanSmemBytes, st>>>((const unsigned int *)in, (unsigned int *)out, n,
-                                                            (unsigned int)seed, d.scratch, counters, d.epoch, tiles);
+                                                            (unsigned int)seed, nullptr, d.scratch, d.epoch, tiles);
   CUXB_LAUNCHED();
   return 0;
+}
+
+// Sharded scan across GPUs (rank r holds the r-th contiguous slice): one reduction kernel whose
+// finishing CTA exchanges the per-GPU totals over NVLink and leaves this rank's exclusive offset in
+// device memory, then the scan kernel, which reads the offset from there.  Two launches, no host
+// synchronisation, no NCCL call.  Replaces MPI_Exscan + local scan
+// (mpi/base_reduce_alltoall_scan.cpp:101 in the reference's MPI tutorial).
+extern "C" int cuxb_mg_exscan_total_i32(cuxb_ctx *, void *, long long, const int32_t *, int32_t *, int, int,
+                                        void *const *);
+CUXB_API int cuxb_mg_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *in, int32_t *out, int world,
+                              int rank, void *const *peer_bufs) {
+  CUXB_REQUIRE(ctx != nullptr, CUXB_ERR_INVALID, "cuxb_mg_scan_i32: null ctx");
+  int rc = cuxb_mg_exscan_total_i32(ctx, stream, n, in, ctx->mg_seed, world, rank, peer_bufs);
+  if (rc) return rc;
+  return scan_entry<unsigned int>("cuxb_mg_scan_i32", ctx, stream, n, (const unsigned int *)in, (unsigned int *)out, 0u,
+                                  (const unsigned int *)ctx->mg_seed);
 }

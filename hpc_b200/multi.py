@@ -60,3 +60,22 @@ def scan_seed(dist, local_total, gathered=None):
     if rank == 0:
         return 0
     return wrap_i32(int(gathered[:rank].to(torch.int64).sum().item()))
+
+
+class PeerExchange:
+    """Per-rank exchange buffers for the fused multi-GPU kernels (cuxb_mg_*), one process per GPU.
+
+    Uses torch's symmetric memory (CUDA IPC / fabric handles under the hood) purely as the plumbing
+    that maps every rank's CUXB_MG_EXCHANGE_BYTES buffer into every process; the exchange itself is
+    done by the reduction kernel's finishing CTA with plain stores and loads on these pointers.
+    """
+
+    def __init__(self, dist, device):
+        import torch.distributed._symmetric_memory as symm
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.buf = symm.empty(64, dtype=torch.int64, device=device)  # 512 bytes >= CUXB_MG_EXCHANGE_BYTES
+        self.buf.zero_()
+        self.handle = symm.rendezvous(self.buf, dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        torch.cuda.synchronize()
+        dist.barrier()  # every buffer is zero before anybody's first exchange

@@ -124,6 +124,35 @@ int cuxb_scan_f32(cuxb_ctx *ctx, void *stream, long long n, const float *in, flo
  * same GPU share the scratch, so two calls whose kernels may run at the same time race. */
 int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in, int32_t *out, int32_t seed);
 
+/* ---- multi-GPU (one process or thread per GPU, all on one NVLink/NVSwitch box).  The scalar
+ * exchange is FUSED into the reduction kernel: every rank's finishing CTA stores its partial into every
+ * rank's exchange buffer through peer-mapped pointers and adds the world's partials in rank order, so
+ * no collective is launched and every rank gets the identical result.  Replaces the
+ * MPI_Allreduce / MPI_Exscan of the reference's MPI tutorials
+ * (/root/reference/mpi/base_reduce_alltoall_scan.cpp:62,101) on GPU partials.
+ *   peer_bufs[r] = rank r's exchange buffer as seen from THIS process (cudaIpc / symmetric memory /
+ *   plain pointers with peer access in a single process), CUXB_MG_EXCHANGE_BYTES each, zero-filled
+ *   once before the first call.  Every rank must make the same sequence of cuxb_mg_* calls.
+ *   world <= 8.  world == 1 degenerates to the single-GPU kernel.  The kernels of different ranks wait
+ *   for each other, so they must be able to run at the same time: one GPU per rank, and -- when one
+ *   process drives several GPUs -- every kernel launched once per device beforehand (its first launch
+ *   loads the module, which can wait for the peer device to go idle).  A rank that never shows up makes
+ *   the others fail with a launch error after 20 s rather than hang. */
+#define CUXB_MG_EXCHANGE_BYTES 256
+int cuxb_mg_dot_f32(cuxb_ctx *ctx, void *stream, long long n, const float *a, const float *b, float *res,
+                    int world, int rank, void *const *peer_bufs);
+int cuxb_mg_sum_f32(cuxb_ctx *ctx, void *stream, long long n, const float *x, float *res, int world, int rank,
+                    void *const *peer_bufs);
+int cuxb_mg_nrm2_f32(cuxb_ctx *ctx, void *stream, long long n, const float *x, float *res, int world, int rank,
+                     void *const *peer_bufs);
+/* *seed_out (device) = sum of the int32 totals of the lower ranks' slices (wrap-around). */
+int cuxb_mg_exscan_total_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *x, int32_t *seed_out,
+                             int world, int rank, void *const *peer_bufs);
+/* Sharded inclusive scan: rank r holds the r-th contiguous slice; out continues the lower ranks' sum. */
+int cuxb_mg_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *in, int32_t *out, int world,
+                     int rank, void *const *peer_bufs);
+int cuxb_enable_peer_access(int device, int peer_device);
+
 /* ---- GEMM: C = alpha * A[M,K] * B[K,N] + beta * C, row-major.
  *
  * cuxb_sgemm_f32 replaces GemmGpuKernelIF::func for TypeFlag::FLOAT32

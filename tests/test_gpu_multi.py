@@ -1,0 +1,96 @@
+"""GPU (needs >= 2 devices, skipped otherwise): the reductions / scan whose cross-GPU exchange is fused into
+the kernel (cuxb_mg_*: partials written into every rank's buffer over NVLink peer memory by the finishing
+CTA).  Single process, two devices, peer access -- each device's kernel waits for the other's partial, both
+are launched asynchronously.  Results must equal the single-device oracle on the concatenated data."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from hpc_b200 import capi
+from hpc_b200 import datagen as dg
+from hpc_b200 import multi
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    L = capi.lib()
+    for a in range(world):
+        for b in range(world):
+            if a != b:
+                capi.check(L.cuxb_enable_peer_access(a, b), "cuxb_enable_peer_access")
+    ctxs = [capi.Context(r) for r in range(world)]
+    bufs = [torch.zeros(64, dtype=torch.int64, device="cuda:%d" % r) for r in range(world)]
+    # Load every kernel on every device BEFORE kernels start waiting on each other: the first launch of
+    # a kernel on a device loads its module, and with peer access enabled that can wait for the other
+    # device to go idle -- which a kernel spinning on a peer's partial never does (single process only).
+    for r in range(world):
+        x = torch.ones(4096, device="cuda:%d" % r)
+        xi = torch.ones(4096, dtype=torch.int32, device="cuda:%d" % r)
+        o = torch.zeros(4096, dtype=torch.int32, device="cuda:%d" % r)
+        c = ctxs[r]
+        c.dot_f32(4096, x.data_ptr(), x.data_ptr(), x.data_ptr())
+        c.sum_f32(4096, x.data_ptr(), x.data_ptr())
+        c.nrm2_f32(4096, x.data_ptr(), x.data_ptr())
+        c.sum_i32(4096, xi.data_ptr(), o.data_ptr())
+        c.scan_i32(4096, xi.data_ptr(), o.data_ptr(), 0)
+        torch.cuda.synchronize(r)
+    return ctxs, bufs, [b.data_ptr() for b in bufs]
+
+
+@pytest.mark.parametrize("world", [2])
+def test_fused_exchange_reductions_and_scan(world):
+    ctxs, bufs, ptrs = _setup(world)
+    n = 3_000_001
+    a, b = dg.int_fill(n, -2, 2, tag=1), dg.int_fill(n, -2, 2, tag=2)
+    x = np.full(n, 3000, np.int32)
+    x[::5] = -7
+    spans = [multi.shard_range(n, world, r) for r in range(world)]
+    da = [torch.from_numpy(a[lo:hi]).to("cuda:%d" % r) for r, (lo, hi) in enumerate(spans)]
+    db = [torch.from_numpy(b[lo:hi]).to("cuda:%d" % r) for r, (lo, hi) in enumerate(spans)]
+    dx = [torch.from_numpy(x[lo:hi]).to("cuda:%d" % r) for r, (lo, hi) in enumerate(spans)]
+    res = [torch.full((1,), -1.0, device="cuda:%d" % r) for r in range(world)]
+    out = [torch.empty_like(t) for t in dx]
+    for rep in range(3):  # repeated calls: epochs / slot parity
+        for r in range(world):
+            ctxs[r].mg_dot_f32(da[r].numel(), da[r].data_ptr(), db[r].data_ptr(), res[r].data_ptr(), world, r, ptrs)
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        for r in range(world):
+            assert float(res[r][0]) == float(oracle.dot_f32(a, b))  # identical on every rank, exact (integer fill)
+    for r in range(world):
+        ctxs[r].mg_sum_f32(da[r].numel(), da[r].data_ptr(), res[r].data_ptr(), world, r, ptrs)
+    for r in range(world):
+        torch.cuda.synchronize(r)
+        assert float(res[r][0]) == float(oracle.sum_f32(a))
+    for r in range(world):
+        ctxs[r].mg_nrm2_f32(da[r].numel(), da[r].data_ptr(), res[r].data_ptr(), world, r, ptrs)
+    for r in range(world):
+        torch.cuda.synchronize(r)
+        assert float(res[r][0]) == float(oracle.nrm2_f32(a))
+    want = oracle.scan_i32(x)
+    assert want.min() < 0
+    for rep in range(2):
+        for r in range(world):
+            ctxs[r].mg_scan_i32(dx[r].numel(), dx[r].data_ptr(), out[r].data_ptr(), world, r, ptrs)
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        got = np.concatenate([o.cpu().numpy() for o in out])
+        assert np.array_equal(got, want)  # bit-exact across the shard boundary, wrap-around included
+
+
+def test_mg_argument_errors():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    c = capi.Context(0)
+    t = torch.zeros(16, device="cuda:0")
+    with pytest.raises(capi.CuxbError):
+        c.mg_dot_f32(16, t.data_ptr(), t.data_ptr(), t.data_ptr(), 9, 0, [0] * 9)  # world > 8
+    with pytest.raises(capi.CuxbError):
+        c.mg_dot_f32(16, t.data_ptr(), t.data_ptr(), t.data_ptr(), 2, 0, [t.data_ptr(), 0])  # null peer buffer
+    # world == 1 degenerates to the single-GPU kernel
+    c.mg_sum_f32(16, t.data_ptr(), t.data_ptr(), 1, 0, [t.data_ptr()])
+    torch.cuda.synchronize()
