@@ -281,3 +281,63 @@ def test_gemm_argument_errors_are_loud():
         c.sgemm_f32(16, 16, 16, 1.0, t.data_ptr(), 8, t.data_ptr(), 16, 0.0, t.data_ptr(), 16)  # lda < K
     with pytest.raises(capi.CuxbError):
         c.linear_s8(16, 16, 8, t.data_ptr(), t.data_ptr(), t.data_ptr())  # K % 16 != 0
+
+
+# ------------------------------------------------------------------ further edge cases
+def test_hgemm_submatrix_leading_dimensions(cta_group):
+    # A, B, C are windows of larger row-major arrays (lda > K, ldb > N, ldc > N), as a caller slicing
+    # a bigger Array4D would pass them
+    M, N, K = 200, 264, 136
+    lda, ldb, ldc = K + 24, N + 40, N + 8
+    Ab = oracle.f32_to_f16(dg.int_fill((M, lda), -10, 9, tag=71))
+    Bb = oracle.f32_to_f16(dg.int_fill((K, ldb), -10, 9, tag=72))
+    Cb = oracle.f32_to_f16(dg.int_fill((M, ldc), -3, 3, tag=73))
+    dA, dB, dC = dev(Ab), dev(Bb), dev(Cb)
+    ctx().hgemm_f16(M, N, K, 1.0, dA.data_ptr(), lda, dB.data_ptr(), ldb, 2.0, dC.data_ptr(), ldc, capi.FLOAT16)
+    sync()
+    got = host(dC, np.uint16)
+    want = oracle.hgemm_f16(np.ascontiguousarray(Ab[:, :K]), np.ascontiguousarray(Bb[:, :N]),
+                            np.ascontiguousarray(Cb[:, :N]), 1.0, 2.0, threads=8)
+    assert np.array_equal(got[:, :N], want)
+    assert np.array_equal(got[:, N:], Cb[:, N:])  # columns outside the window untouched
+
+
+@pytest.mark.parametrize("K", [8, 56, 64, 72, 4104])
+def test_hgemm_k_tails(K, cta_group):
+    M, N = 130, 264
+    A16 = oracle.f32_to_f16(dg.int_fill((M, K), -4, 4, tag=74))
+    B16 = oracle.f32_to_f16(dg.int_fill((K, N), -4, 4, tag=75))
+    assert np.array_equal(run_hgemm(A16, B16, c_f32=True), oracle.hgemm_f16(A16, B16, c_f32=True, threads=8))
+
+
+def test_int8_extremes_and_minimal_k(cta_group):
+    # -128 * -128 summed over K: the largest magnitudes the accumulator sees
+    for (M, N, K), fill in (((128, 256, 8192), -128), ((16, 16, 16), 127), ((3, 4, 16), -128)):
+        A = np.full((M, K), fill, np.int8)
+        B = np.full((N, K), -128, np.int8)
+        B[::2] = 127
+        dA, dB = dev(A), dev(B)
+        dC = torch.zeros((M, N), dtype=torch.int32, device="cuda")
+        ctx().linear_s8(M, N, K, dA.data_ptr(), dB.data_ptr(), dC.data_ptr())
+        sync()
+        assert np.array_equal(host(dC), oracle.linear_s8(A, B, threads=8))
+
+
+def test_linear_bf16_normal_fill_large_within_one_ulp(cta_group):
+    M, N, K = 512, 512, 2048
+    A16 = oracle.f32_to_bf16(dg.normal_fill((M, K), tag=76))
+    B16 = oracle.f32_to_bf16(dg.normal_fill((N, K), tag=77))
+    dA, dB = dev(A16), dev(B16)
+    dC = torch.zeros((M, N), dtype=torch.float32, device="cuda")
+    ctx().linear_bf16(M, N, K, dA.data_ptr(), dB.data_ptr(), dC.data_ptr(), capi.FLOAT32)
+    sync()
+    want = oracle.linear_bf16(A16, B16, c_f32=True, threads=8)
+    # bf16 products are exact in fp32; only the order of the fp32 additions differs
+    assert np.max(np.abs(host(dC) - want)) <= 1e-5 * np.sqrt(K) * 16
+
+
+def test_sgemm_alpha_zero_and_beta_one_leave_c():
+    M, N, K = 256, 128, 64
+    A, B, C = dg.uniform_fill((M, K), tag=78), dg.uniform_fill((K, N), tag=79), dg.uniform_fill((M, N), tag=80)
+    assert np.array_equal(run_sgemm(A, B, C, 0.0, 1.0), C)
+    assert np.array_equal(run_sgemm(A, B, C, 0.0, 0.0), np.zeros_like(C))
