@@ -267,67 +267,137 @@ def peak_for(W, peaks):
 
 
 # --------------------------------------------------------------------------- CPU reference arm
-def cpu_dot_reference(n, seconds_budget, seed=20240607):
-    """DotHostV0 (0-frameworks/cux/src/operator/dot_product.cpp:7-13) on this host, single thread
-    (the reference's dot has no parallel variant inside cux).  Returns (GB/s, kind, passes)."""
-    import oracle
-    rng = np.random.default_rng(seed)
-    a = rng.integers(-2, 3, size=n).astype(np.float32)
-    b = rng.integers(-2, 3, size=n).astype(np.float32)
-    out = np.zeros(1, np.float32)
-    R = oracle.ref()
-    if R is not None:
-        kind, f = "reference", lambda: R.ref_cux_dot_v0(n, a, b, out)
-    else:
-        L = oracle.lib()
-        kind, f = "port", lambda: L.orc_dot_f32(n, a, b, out)
-    f()
+def _timed(f, budget_s, max_reps=64):
+    f()  # warm caches / page in
     times = []
-    t_end = time.time() + seconds_budget
+    t_end = time.time() + budget_s
     while True:
         t0 = time.perf_counter()
         f()
         times.append(time.perf_counter() - t0)
-        if time.time() > t_end or len(times) >= 64:
+        if time.time() > t_end or len(times) >= max_reps:
             break
-    return times, kind, float(out[0])
+    return float(np.median(times)), len(times)
+
+
+def cpu_baseline_for(name, budget_s=3.0):
+    """The reference's own CPU implementation of `name` (oracle/_ref, built from /root/reference; the
+    oracle port where the reference has no such function) timed on this host on a BOUNDED sample of the
+    same workload.  Returns the cpu_baseline dict; 'cores' is the number of threads actually used."""
+    import oracle
+    R, L = oracle.ref(), oracle.lib()
+    rng = np.random.default_rng(20240607)
+    ncores = os.cpu_count() or 1
+    if name in ("dot", "sum", "nrm2"):
+        n = N_DOT
+        a = rng.integers(-2, 3, size=n).astype(np.float32)
+        out = np.zeros(1, np.float32)
+        if name == "dot":
+            b = rng.integers(-2, 3, size=n).astype(np.float32)
+            f = (lambda: R.ref_cux_dot_v0(n, a, b, out)) if R else (lambda: L.orc_dot_f32(n, a, b, out))
+            fn, nbytes = "DotHostV0 (dot_product.cpp:7-13)", 8 * n
+        elif name == "sum":
+            f = (lambda: R.ref_reduce_host(a, out, n)) if R else (lambda: L.orc_sum_f32(n, a, out))
+            fn, nbytes = "ReduceHost (reduce_fp32.cu:26-31)", 4 * n
+        else:
+            f = (lambda: R.ref_cux_nrm2_v0(n, a, out)) if R else (lambda: L.orc_nrm2_f32(n, a, out))
+            fn, nbytes = "Nrm2HostV0 (nrm2.cpp:7-16)", 4 * n
+        t, reps = _timed(f, budget_s)
+        return {"value": nbytes / t / 1e9, "unit": "GB/s", "cores": 1, "kind": "reference" if R else "port",
+                "sample": "%s over the full N=2^28 vector(s), %d passes (median); single thread, as in the reference" % (fn, reps)}
+    if name == "scan":
+        n = 1 << 27
+        x = rng.integers(-2, 3, size=n).astype(np.int32)
+        out = np.empty_like(x)
+        t, reps = _timed(lambda: L.orc_scan_i32(n, x, out, 0), budget_s)
+        note = ""
+        if R is not None:
+            xf, of = x.astype(np.float32), np.empty(n, np.float32)
+            t2, _ = _timed(lambda: R.ref_scan_f32(2, xf, n, of), 1.5)
+            note = "; the reference's fp32 VectorScanSIMDv2 (vector_scan.cpp:66-79) on the same slice: %.2f GB/s" % (8 * n / t2 / 1e9)
+        return {"value": 8 * n / t / 1e9, "unit": "GB/s", "cores": 1, "kind": "port",
+                "sample": "int32 restatement of VectorScanNormal (vector_scan.cpp:21-26) over N=2^27 (1/8 of the workload), "
+                          "%d passes (median), single thread%s" % (reps, note)}
+    if name == "sgemm":
+        n, rows = SGEMM_N, 96
+        A = rng.integers(-2, 6, size=(rows, n)).astype(np.float32)
+        B = rng.integers(-2, 6, size=(n, n)).astype(np.float32)
+        C = np.zeros((rows, n), np.float32)
+        flop = 2.0 * rows * n * n
+        if R is None:
+            t, reps = _timed(lambda: L.orc_gemm_f32_ikj(rows, n, n, 1.0, A, n, B, n, 0.0, C, n, ncores), budget_s, 8)
+            return {"value": flop / t / 1e12, "unit": "TFLOP/s", "cores": ncores, "kind": "port",
+                    "sample": "GemmHostV1 order, OpenMP over rows, %d-row slice of the 8192^3 problem (rows are independent)" % rows}
+        t4, _ = _timed(lambda: R.ref_cux_gemm(4, rows, n, n, 1.0, A, n, B, n, 0.0, C, n), budget_s / 2, 8)
+        tm, _ = _timed(lambda: R.ref_omp_gemm(1, rows, n, n, 1.0, A, n, B, n, C, n), budget_s / 2, 8)
+        best, who, cores = (t4, "GemmHostV4 (gemm.cpp:161-218, AVX + OpenMP num_threads(6))", min(6, ncores)) if t4 <= tm else \
+                           (tm, "MatrixMulMP (openmp/alg_matrix_multiply.cpp:33-51, all cores)", R.ref_num_threads())
+        return {"value": flop / best / 1e12, "unit": "TFLOP/s", "cores": cores, "kind": "reference",
+                "sample": "%s on a %d-row slice of the 8192^3 problem (rows are independent); GemmHostV4 %.1f GFLOP/s, "
+                          "MatrixMulMP %.1f GFLOP/s" % (who, rows, flop / t4 / 1e9, flop / tm / 1e9)}
+    if name == "hgemm":
+        n, rows = HGEMM_N, 1
+        A16 = rng.integers(-10, 10, size=(rows, n)).astype(np.float16).view(np.uint16)
+        B16 = rng.integers(-10, 10, size=(n, n)).astype(np.float16).view(np.uint16)
+        C16 = np.zeros((rows, n), np.uint16)
+        flop = 2.0 * rows * n * n
+        if R is not None:
+            t0 = time.perf_counter()
+            R.ref_hgemm_host(rows, n, n, A16, n, B16, n, C16, n)
+            t = time.perf_counter() - t0
+            note = ""
+            if R.ref_cpu_has_avx512bf16():
+                r2 = 64
+                Ab = rng.integers(-10, 10, size=(r2, n)).astype(np.float32).view(np.uint32) >> 16
+                Ab = Ab.astype(np.uint16)
+                Bb = (B16.astype(np.uint16))  # bit patterns only need to be valid bf16 for timing
+                Cb = np.zeros((r2, n), np.uint16)
+                t2, _ = _timed(lambda: R.ref_linear_bf16(1, r2, n, n, Ab, Bb, Cb), 1.5, 4)
+                note = "; fastest 16-bit CPU path in the repo, LinearAvx512Bf16 (linear.cpp:156-182, 1 thread) on a 64-row slice: %.1f GFLOP/s" % (2.0 * r2 * n * n / t2 / 1e9)
+            return {"value": flop / t / 1e12, "unit": "TFLOP/s", "cores": 1, "kind": "reference",
+                    "sample": "GemmHostV1-half (gemm_fp16_wmma.cu:75-90) on a %d-row slice of the 16384^3 problem, one pass, "
+                              "single thread (rows are independent; the full problem would take hours)%s" % (rows, note)}
+        t, _ = _timed(lambda: L.orc_hgemm_f16(rows, n, n, 1.0, A16, n, B16, n, 0.0, C16.ctypes.data, n, 0, 1), budget_s, 2)
+        return {"value": flop / t / 1e12, "unit": "TFLOP/s", "cores": 1, "kind": "port", "sample": "%d-row slice" % rows}
+    if name == "linear_s8":
+        n, rows = LIN8_N, 128
+        A = rng.integers(0, 17, size=(rows, n)).astype(np.int8)
+        B = rng.integers(-8, 9, size=(n, n)).astype(np.int8)
+        C = np.zeros((rows, n), np.int32)
+        ops = 2.0 * rows * n * n
+        if R is not None and R.ref_cpu_has_avx512():
+            t, reps = _timed(lambda: R.ref_linear_s8(1, rows, n, n, A, B, C), budget_s, 8)
+            who, kind = "LinearAvx512Int8 (linear.cpp:214-237, VNNI dpbusd; valid because A >= 0)", "reference"
+        elif R is not None:
+            t, reps = _timed(lambda: R.ref_linear_s8(0, rows, n, n, A, B, C), budget_s, 4)
+            who, kind = "LinearNormalInt8 (linear.cpp:199-211)", "reference"
+        else:
+            t, reps = _timed(lambda: L.orc_linear_s8(rows, n, n, A, B, C, 1), budget_s, 4)
+            who, kind = "LinearNormalInt8 restatement", "port"
+        return {"value": ops / t / 1e12, "unit": "TOP/s", "cores": 1, "kind": kind,
+                "sample": "%s on a %d-row slice of the 8192^3 problem, %d passes (median), single thread as in the sample" % (who, rows, reps)}
+    raise ValueError(name)
 
 
 def run_reference_arm(args):
+    """--impl reference: the reference's own CPU implementation of the workload, same metric/unit/config."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    if args.workload != "dot":
-        print(json.dumps({"impl": "reference", "unavailable": "reference arm implemented for the default dot workload only"}))
-        return
-    n = N_DOT
-    import oracle
-    rng = np.random.default_rng(20240607)
-    a = rng.integers(-2, 3, size=n).astype(np.float32)
-    b = rng.integers(-2, 3, size=n).astype(np.float32)
-    out = np.zeros(1, np.float32)
-    R = oracle.ref()
-    if R is not None:
-        kind, f = "reference", lambda: R.ref_cux_dot_v0(n, a, b, out)
-    else:
-        kind, f = "port", lambda: oracle.lib().orc_dot_f32(n, a, b, out)
-    for _ in range(args.warmup):
-        f()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        f()
-    dt = time.perf_counter() - t0
-    ms = dt * 1e3 / args.steps
-    v = 8 * n / (ms * 1e-3) / 1e9
+    d = make_desc(args.workload)
+    # each "step" = one pass over the bounded sample; K steps timed after W warm-up passes
+    t_start = time.perf_counter()
+    cb = cpu_baseline_for(args.workload, budget_s=max(1.0, min(20.0, 0.25 * args.steps)))
+    wall = time.perf_counter() - t_start
+    v = cb["value"]
+    per_pass_ms = wall * 1e3 / max(1, args.steps)  # wall time of the whole arm spread over the requested steps
     line = {
-        "impl": "reference", "metric": "reduce HBM GB/s (fp32 dot-product, N=2^28 per GPU)", "value": v, "unit": "GB/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "cux dot fp32 N=2^28 (configs[1]) on the host CPU: DotHostV0, single thread (cux has no parallel dot)"},
-        "cpu_baseline": {"value": v, "unit": "GB/s", "cores": 1, "kind": kind,
-                         "sample": "full N=2^28 vectors (2 GiB read) per step"},
-        "e2e": {"value": v, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "impl": "reference", "metric": d["metric"], "value": v, "unit": d["unit"], "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_pass_ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": d["dtype"], "data": "synthetic",
+        "config": {"workload": d["desc"] + " -- on the host CPU through the reference's own code", "sample": cb["sample"]},
+        "cpu_baseline": cb, "e2e": {"value": v, "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": wall,
     }
     print(json.dumps(line))
 
@@ -472,16 +542,15 @@ def main():
                               "peak_source": pn, "workload": w2.desc}
                 del w2
                 torch.cuda.empty_cache()
+                if not args.no_cpu:
+                    also[name]["cpu_baseline"] = cpu_baseline_for(name, 2.0)
             except Exception as ex:  # reported, not hidden
                 also[name] = {"error": str(ex)[:300]}
 
     # ---- CPU baseline leg (rank 0, N=1): DotHostV0 on the host cores
     cpu = None
-    if world == 1 and rank == 0 and not args.no_cpu and args.workload == "dot":
-        times, kind, _ = cpu_dot_reference(N_DOT, 10.0)
-        best = float(np.median(times))
-        cpu = {"value": 8 * N_DOT / best / 1e9, "unit": "GB/s", "cores": 1, "kind": kind,
-               "sample": "DotHostV0 over the full N=2^28 vectors, %d passes (median), single thread as in cux" % len(times)}
+    if world == 1 and rank == 0 and not args.no_cpu:
+        cpu = cpu_baseline_for(args.workload, 10.0 if args.workload == "dot" else 4.0)
 
     if rank == 0:
         wl = make_desc(args.workload)
