@@ -63,6 +63,7 @@ SIGNATURES = {
     "cuxb_mg_nrm2_f32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
     "cuxb_mg_exscan_total_i32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
     "cuxb_mg_scan_i32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
+    "cuxb_mg_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i], _i),
     "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
@@ -192,6 +193,11 @@ class Context:
 
     def mg_scan_i32(self, n, src, dst, world, rank, peer_ptrs, stream=0):
         check(lib().cuxb_mg_scan_i32(self._h, stream, n, src, dst, world, rank, self._peers(peer_ptrs)), "cuxb_mg_scan_i32")
+
+    def mg_hgemm_f16(self, M, N, K, alpha, A, lda, b_root, b_local, ldb, beta, Cp, ldc, is_root, c_dtype=FLOAT16,
+                     stream=0):
+        check(lib().cuxb_mg_hgemm_f16_f32acc(self._h, stream, M, N, K, alpha, A, lda, b_root, b_local, ldb, beta, Cp,
+                                             ldc, c_dtype, int(is_root)), "cuxb_mg_hgemm_f16_f32acc")
 
     def convert(self, n, src, src_dtype, dst, dst_dtype, stream=0):
         check(lib().cuxb_convert(self._h, stream, n, src, src_dtype, dst, dst_dtype), "cuxb_convert")

@@ -49,13 +49,12 @@ constexpr int kScanTileElems = 8192;                 // 512 threads x 16 ints
 constexpr long long kScanMaxTiles = (1ll << 31) / kScanTileElems;  // n < 2^31 (cux uses int lengths)
 constexpr int kReduceMaxBlocks = 2048;
 
+// A cuTensorMapEncodeTiled result, keyed by everything that went into it.
 struct TmaCacheEntry {
   const void *base;
-  uint64_t dims[2];
-  uint64_t stride1;
-  uint32_t box[2];
-  int dtype_bytes;
-  int swizzle;
+  uint64_t rows, cols, ld;
+  uint32_t box_cols, box_rows;
+  int dtype;
   alignas(64) unsigned char map[128];
 };
 
@@ -70,17 +69,19 @@ struct cuxb_ctx {
   unsigned int *red_ticket;  // zero at rest
   // scan: tile states (64-bit), dynamic tile counter, launch epoch
   unsigned long long *scan_state;
-  unsigned int *scan_counter;  // [0] tile ticket, [1] finished tiles
   long long scan_state_tiles;
   unsigned int scan_epoch;
   unsigned int mg_epoch;       // multi-GPU exchange epoch (all ranks make the same sequence of mg calls)
   int *mg_seed;                // device int32: the sharded scan's exclusive offset
+  unsigned int *bcast_ready;   // fused B broadcast: per-panel arrival counters (grow by grid size per call)
+  unsigned int bcast_calls;
+  int bcast_grid;
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];
   cudaStream_t stage_stream;
   // TMA descriptor cache
-  cuxb::TmaCacheEntry tma_cache[16];
+  cuxb::TmaCacheEntry tma_cache[16];  // most recent TMA descriptors (encoding one costs microseconds)
   int tma_cache_n;
   int tma_cache_next;
   std::mutex *mu;

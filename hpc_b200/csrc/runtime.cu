@@ -72,8 +72,6 @@ CUXB_API int cuxb_ctx_create(int device, cuxb_ctx **out) {
   e = cudaMalloc(&c->red_partials, kReduceMaxBlocks * 8);
   if (e == cudaSuccess) e = cudaMalloc((void **)&c->red_ticket, 256);
   if (e == cudaSuccess) e = cudaMemset(c->red_ticket, 0, 256);
-  if (e == cudaSuccess) e = cudaMalloc((void **)&c->scan_counter, 256);
-  if (e == cudaSuccess) e = cudaMemset(c->scan_counter, 0, 256);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->stage_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
@@ -95,7 +93,7 @@ CUXB_API int cuxb_ctx_destroy(cuxb_ctx *c) {
   if (c->red_partials) cudaFree(c->red_partials);
   if (c->red_ticket) cudaFree(c->red_ticket);
   if (c->scan_state) cudaFree(c->scan_state);
-  if (c->scan_counter) cudaFree(c->scan_counter);
+  if (c->bcast_ready) cudaFree(c->bcast_ready);
   for (int i = 0; i < 4; i++)
     if (c->stage[i]) cudaFree(c->stage[i]);
   if (c->stage_stream) cudaStreamDestroy(c->stage_stream);

@@ -79,3 +79,17 @@ class PeerExchange:
         self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
         torch.cuda.synchronize()
         dist.barrier()  # every buffer is zero before anybody's first exchange
+
+    def symmetric_like(self, t):
+        """A symmetric (peer-mapped) tensor with t's shape/dtype on every rank: .tensor is this rank's
+        instance, .ptrs[r] is rank r's instance as mapped into this process."""
+        import torch.distributed._symmetric_memory as symm
+        import torch.distributed as dist
+
+        class _Sym:
+            pass
+        out = _Sym()
+        out.tensor = symm.empty(tuple(t.shape), dtype=t.dtype, device=t.device)
+        out.handle = symm.rendezvous(out.tensor, dist.group.WORLD)
+        out.ptrs = [int(p) for p in out.handle.buffer_ptrs]
+        return out

@@ -151,6 +151,16 @@ int cuxb_mg_exscan_total_i32(cuxb_ctx *ctx, void *stream, long long n, const int
 /* Sharded inclusive scan: rank r holds the r-th contiguous slice; out continues the lower ranks' sum. */
 int cuxb_mg_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *in, int32_t *out, int world,
                      int rank, void *const *peer_bufs);
+/* Row-sharded fp16 GEMM with the broadcast of B fused into the kernel (the MPI GEMM of
+ * /root/reference/mpi/alg_matrix_multiply.cpp:52-74 -- B to every worker, row blocks of A and C -- without a
+ * separate send): the root rank (is_root != 0) multiplies with b_root in place; any other rank passes the
+ * root's B as mapped into its address space (b_root) and a local buffer of the same shape (b_local) that
+ * the kernel fills over NVLink, column panel by column panel, while it is already multiplying the panels
+ * that have arrived.  Same requirements as cuxb_hgemm_f16_f32acc.  The root must leave B untouched until
+ * every rank's call has finished. */
+int cuxb_mg_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const void *A,
+                             int lda, const void *b_root, void *b_local, int ldb, float beta, void *C, int ldc,
+                             int c_dtype, int is_root);
 int cuxb_enable_peer_access(int device, int peer_device);
 
 /* ---- GEMM: C = alpha * A[M,K] * B[K,N] + beta * C, row-major.

@@ -94,3 +94,34 @@ def test_mg_argument_errors():
     # world == 1 degenerates to the single-GPU kernel
     c.mg_sum_f32(16, t.data_ptr(), t.data_ptr(), 1, 0, [t.data_ptr()])
     torch.cuda.synchronize()
+
+
+def test_fused_b_broadcast_gemm_two_gpus():
+    """Row-sharded fp16 GEMM: rank 0 owns B, rank 1's kernel pulls B over NVLink while it multiplies."""
+    world = 2
+    ctxs, _, _ = _setup(world)
+    M, N, K = 1024, 2304, 1000  # ragged: N not a multiple of 256, K not a multiple of 24 or 64
+    A = [oracle.f32_to_f16(dg.int_fill((M, K), -10, 9, tag=90 + r)) for r in range(world)]
+    B16 = oracle.f32_to_f16(dg.int_fill((K, N), -10, 9, tag=95))
+    dev = lambda x, r: torch.from_numpy(np.ascontiguousarray(x).view(np.int16)).to("cuda:%d" % r)
+    dA = [dev(A[r], r) for r in range(world)]
+    dB_root = dev(B16, 0)
+    dB_local = torch.zeros((K, N), dtype=torch.int16, device="cuda:1")
+    dC = [torch.zeros((M, N), dtype=torch.int16, device="cuda:%d" % r) for r in range(world)]
+    # load the GEMM kernel on both devices before anything waits on a peer (see _setup)
+    for r in range(world):
+        ctxs[r].hgemm_f16(M, N, K, 1.0, dA[r].data_ptr(), K, (dB_root if r == 0 else dB_local).data_ptr(), N, 0.0,
+                          dC[r].data_ptr(), N, capi.FLOAT16)
+        torch.cuda.synchronize(r)
+    for rep in range(3):
+        dB_local.zero_()
+        torch.cuda.synchronize(1)
+        ctxs[0].mg_hgemm_f16(M, N, K, 1.0, dA[0].data_ptr(), K, dB_root.data_ptr(), 0, N, 0.0, dC[0].data_ptr(), N, True)
+        ctxs[1].mg_hgemm_f16(M, N, K, 1.0, dA[1].data_ptr(), K, dB_root.data_ptr(), dB_local.data_ptr(), N, 0.0,
+                             dC[1].data_ptr(), N, False)
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        assert np.array_equal(dB_local.cpu().numpy().view(np.uint16), B16)  # the broadcast itself
+        for r in range(world):
+            want = oracle.hgemm_f16(A[r], B16, threads=8)
+            assert np.array_equal(dC[r].cpu().numpy().view(np.uint16), want), "rank %d rep %d" % (r, rep)
