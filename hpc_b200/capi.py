@@ -67,6 +67,7 @@ SIGNATURES = {
     "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
+    "cuxb_gemm_bf16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
     "cuxb_linear_s8_s32": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp], _i),
     "cuxb_linear_bf16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i], _i),
     "cuxb_linear_f16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i], _i),
@@ -165,6 +166,10 @@ class Context:
     def hgemm_f16(self, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc, c_dtype=FLOAT16, stream=0):
         check(lib().cuxb_hgemm_f16_f32acc(self._h, stream, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc,
                                           c_dtype), "cuxb_hgemm_f16_f32acc")
+
+    def gemm_bf16(self, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc, c_dtype=BFLOAT16, stream=0):
+        check(lib().cuxb_gemm_bf16_f32acc(self._h, stream, M, N, K, alpha, A, lda, B, ldb, beta, Cp, ldc,
+                                          c_dtype), "cuxb_gemm_bf16_f32acc")
 
     def linear_s8(self, M, N, K, A, Bt, Cp, stream=0):
         check(lib().cuxb_linear_s8_s32(self._h, stream, M, N, K, A, Bt, Cp), "cuxb_linear_s8_s32")

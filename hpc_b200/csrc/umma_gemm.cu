@@ -704,6 +704,22 @@ CUXB_API int cuxb_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, in
   return dispatch_cg<KIND_F16, true, CUXB_FLOAT32>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
 }
 
+// bf16 operands in cux's gemm layout (B[K,N]); the reference's TypeFlag has no bf16 (util.h:22-28) --
+// this is the bf16 twin of the FLOAT16 gemm kernel, same tcgen05 pipeline with bf16 instruction format.
+CUXB_API int cuxb_gemm_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const void *A,
+                                   int lda, const void *B, int ldb, float beta, void *C, int ldc, int c_dtype) {
+  CUXB_REQUIRE(c_dtype == CUXB_BFLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,
+               "cuxb_gemm_bf16_f32acc: c_dtype must be CUXB_BFLOAT16 or CUXB_FLOAT32");
+  int rc = check_common("cuxb_gemm_bf16_f32acc", ctx, M, N, K, A, B, C, 2, lda, ldb, ldc,
+                        c_dtype == CUXB_BFLOAT16 ? 2 : 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  CUXB_REQUIRE(lda >= K && ldb >= N && ldc >= N, CUXB_ERR_INVALID, "cuxb_gemm_bf16_f32acc: leading dimension too small");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c_dtype == CUXB_BFLOAT16)
+    return dispatch_cg<KIND_BF16, true, CUXB_BFLOAT16>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+  return dispatch_cg<KIND_BF16, true, CUXB_FLOAT32>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
+}
+
 CUXB_API int cuxb_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A, const void *Bt,
                                     void *C, int c_dtype) {
   CUXB_REQUIRE(c_dtype == CUXB_FLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,

@@ -178,6 +178,11 @@ int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha
 int cuxb_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha,
                           const void *A, int lda, const void *B, int ldb, float beta, void *C,
                           int ldc, int c_dtype);
+/* The same with bf16 operands (c_dtype CUXB_BFLOAT16 or CUXB_FLOAT32); numerically the contraction of
+ * LinearNormalBf16 (simd/x86/linear.cpp:137-151) in cux's B[K,N] layout. */
+int cuxb_gemm_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha,
+                          const void *A, int lda, const void *B, int ldb, float beta, void *C,
+                          int ldc, int c_dtype);
 
 /* ---- linear: C[M,N] = A[M,K] * Bt[N,K]^T (simd/x86/linear.cpp:2).
  * cuxb_linear_s8_s32 replaces LinearNormalInt8 / LinearAvx512Int8

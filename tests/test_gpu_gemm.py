@@ -341,3 +341,21 @@ def test_sgemm_alpha_zero_and_beta_one_leave_c():
     A, B, C = dg.uniform_fill((M, K), tag=78), dg.uniform_fill((K, N), tag=79), dg.uniform_fill((M, N), tag=80)
     assert np.array_equal(run_sgemm(A, B, C, 0.0, 1.0), C)
     assert np.array_equal(run_sgemm(A, B, C, 0.0, 0.0), np.zeros_like(C))
+
+
+def test_gemm_bf16_cux_layout(cta_group):
+    # bf16 operands, B stored [K,N] like cux's gemm: equals LinearNormalBf16 on B^T
+    M, N, K = 384, 520, 200
+    Af, Bf = dg.int_fill((M, K), -6, 6, tag=81), dg.int_fill((K, N), -6, 6, tag=82)
+    A16, B16 = oracle.f32_to_bf16(Af), oracle.f32_to_bf16(Bf)
+    want = oracle.linear_bf16(A16, np.ascontiguousarray(B16.T), threads=8)
+    dA, dB = dev(A16), dev(B16)
+    dC = torch.zeros((M, N), dtype=torch.int16, device="cuda")
+    ctx().gemm_bf16(M, N, K, 1.0, dA.data_ptr(), K, dB.data_ptr(), N, 0.0, dC.data_ptr(), N)
+    sync()
+    assert np.array_equal(host(dC, np.uint16), want)
+    want32 = oracle.linear_bf16(A16, np.ascontiguousarray(B16.T), c_f32=True, threads=8)
+    dC32 = torch.zeros((M, N), dtype=torch.float32, device="cuda")
+    ctx().gemm_bf16(M, N, K, 1.0, dA.data_ptr(), K, dB.data_ptr(), N, 0.0, dC32.data_ptr(), N, capi.FLOAT32)
+    sync()
+    assert np.array_equal(host(dC32), want32)
