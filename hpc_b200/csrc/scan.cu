@@ -20,6 +20,8 @@
 //
 // Scratch memory: 8 bytes per tile (1 KiB per Mi elements), owned by the
 // cuxb_ctx.  Launches that share a ctx must not overlap.
+#include <string.h>
+
 #include "common.cuh"
 
 namespace cuxb {
@@ -355,6 +357,29 @@ scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed
   }
 }
 
+// The CTAs of one scan wait on each other's aggregates, so they must all be resident at once.  A
+// cooperative launch makes the driver guarantee that (or refuse): two scans issued on different
+// streams are then run one after the other instead of interleaving into a dead wait.
+template <typename T>
+static int launch_scan(cudaStream_t st, unsigned int grid, const T *in, T *out, long long n, T seed, const T *seed_ptr,
+                       unsigned long long *state, unsigned int epoch, unsigned int tiles) {
+  CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(kScanCtaThreads, 1, 1);
+  cfg.dynamicSmemBytes = kScanSmemBytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CUXB_CUDA(cudaLaunchKernelEx(&cfg, scan_kernel<T>, in, out, n, seed, seed_ptr, state, epoch, tiles));
+  g_launches.fetch_add(1);
+  return 0;
+}
+
 template <typename T>
 static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n, const T *in, T *out,
                       T seed, const T *seed_ptr = nullptr) {
@@ -390,11 +415,8 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
   }
   long long grid = (long long)ctx->sm_count * kScanCtasPerSM;  // all CTAs resident (see scan_kernel)
   if (grid > tiles) grid = tiles;
-  CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
-  scan_kernel<T><<<(unsigned int)grid, kScanCtaThreads, kScanSmemBytes, st>>>(in, out, n, seed, seed_ptr, ctx->scan_state,
-                                                               ctx->scan_epoch, (unsigned int)tiles);
-  CUXB_LAUNCHED();
-  return 0;
+  return launch_scan<T>(st, (unsigned int)grid, in, out, n, seed, seed_ptr, ctx->scan_state, ctx->scan_epoch,
+                        (unsigned int)tiles);
 }
 
 const void *scan_kernel_symbol() { return (const void *)scan_kernel<unsigned int>; }
@@ -489,11 +511,8 @@ CUXB_API int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in,
   const unsigned int tiles = (unsigned int)div_up(n, kScanTileElems);
   unsigned int grid = (unsigned int)d.sm_count * kScanCtasPerSM;  // every CTA resident at once
   if (grid > tiles) grid = tiles;
-  CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<unsigned int>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
-  scan_kernel<unsigned int><<<grid, kScanCtaThreads, kScanSmemBytes, st>>>((const unsigned int *)in, (unsigned int *)out, n,
-                                                            (unsigned int)seed, nullptr, d.scratch, d.epoch, tiles);
-  CUXB_LAUNCHED();
-  return 0;
+  return launch_scan<unsigned int>(st, grid, (const unsigned int *)in, (unsigned int *)out, n, (unsigned int)seed,
+                                   (const unsigned int *)nullptr, d.scratch, d.epoch, tiles);
 }
 
 // Sharded scan across GPUs (rank r holds the r-th contiguous slice): one reduction kernel whose

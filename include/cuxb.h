@@ -109,7 +109,9 @@ int cuxb_sum_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *x, int
 /* ---- inclusive prefix scan, out[i] = seed + in[0] + ... + in[i], int32 with
  * wrap-around.  Replaces VectorScanNormal/SIMDv1/SIMDv2
  * (simd/x86/vector_scan.cpp:21-79) in the int element type of
- * tbb/base_parallel_scan.cpp:62-65.  in == out (in place) is allowed. */
+ * tbb/base_parallel_scan.cpp:62-65.  in == out (in place) is allowed.  The kernel is launched
+ * cooperatively (its CTAs wait on each other's tile totals), so scans issued on different streams of
+ * one GPU run one after the other. */
 int cuxb_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *in, int32_t *out, int32_t seed);
 /* fp32 variant (same recurrence; the order of additions differs from the serial
  * reference). */

@@ -359,3 +359,34 @@ def test_gemm_bf16_cux_layout(cta_group):
     ctx().gemm_bf16(M, N, K, 1.0, dA.data_ptr(), K, dB.data_ptr(), N, 0.0, dC32.data_ptr(), N, capi.FLOAT32)
     sync()
     assert np.array_equal(host(dC32), want32)
+
+
+def test_hgemm_n_and_k_not_multiples_of_eight(cta_group):
+    # only the row pitches have to be 16-byte multiples; N and K themselves may be ragged
+    M, N, K, ld = 70, 20, 20, 24
+    Ab = oracle.f32_to_f16(dg.int_fill((M, ld), -10, 9, tag=83))
+    Bb = oracle.f32_to_f16(dg.int_fill((K, ld), -10, 9, tag=84))
+    Cb = oracle.f32_to_f16(dg.int_fill((M, ld), -3, 3, tag=85))
+    dA, dB, dC = dev(Ab), dev(Bb), dev(Cb)
+    ctx().hgemm_f16(M, N, K, 1.0, dA.data_ptr(), ld, dB.data_ptr(), ld, 1.0, dC.data_ptr(), ld, capi.FLOAT16)
+    sync()
+    got = host(dC, np.uint16)
+    want = oracle.hgemm_f16(np.ascontiguousarray(Ab[:, :K]), np.ascontiguousarray(Bb[:, :N]),
+                            np.ascontiguousarray(Cb[:, :N]), 1.0, 1.0)
+    assert np.array_equal(got[:, :N], want) and np.array_equal(got[:, N:], Cb[:, N:])
+
+
+def test_two_scans_on_two_streams_do_not_deadlock():
+    # the scan's CTAs wait on each other; the cooperative launch makes concurrent scans take turns
+    c1, c2 = ctx(), capi.Context(0)
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    x = dg.int_fill(1 << 24, -2, 2, np.int32, tag=86)
+    d = dev(x)
+    o1, o2 = torch.empty_like(d), torch.empty_like(d)
+    torch.cuda.synchronize()
+    for _ in range(4):
+        c1.scan_i32(x.size, d.data_ptr(), o1.data_ptr(), 1, s1.cuda_stream)
+        c2.scan_i32(x.size, d.data_ptr(), o2.data_ptr(), 2, s2.cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(host(o1), oracle.scan_i32(x, 1)) and np.array_equal(host(o2), oracle.scan_i32(x, 2))
+    c2.close()
