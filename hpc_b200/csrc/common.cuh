@@ -76,6 +76,9 @@ struct cuxb_ctx {
   unsigned int *bcast_ready;   // fused B broadcast: per-panel arrival counters (grow by grid size per call)
   unsigned int bcast_calls;
   int bcast_grid;
+  // sgemm split-K: parked accumulators + per-tile tickets
+  void *sg_scratch;
+  size_t sg_scratch_bytes;
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];

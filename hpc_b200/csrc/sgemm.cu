@@ -41,6 +41,12 @@ struct SgemmArgs {
   float *C;
   int ldc;
   int tiles_m, tiles_n;
+  // split-K (problems with fewer tiles than the GPU has room for): CTA = (tile, split); split s
+  // multiplies k in [s*k_per_split, (s+1)*k_per_split), parks its accumulators in `scratch`, and the
+  // last CTA to finish a tile adds the splits in index order and runs the epilogue.
+  int splits, k_per_split;
+  float4 *scratch;        // [tile][split][16][256] float4
+  unsigned int *tickets;  // [tile], zero at rest
 };
 
 template <bool FAST>
@@ -61,7 +67,10 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   const int tn0 = warp_n * 32 + lane_n * 4;
 
   // grouped rasterisation
-  const int pid = blockIdx.x;
+  const int pid = blockIdx.x / p.splits;
+  const int split = blockIdx.x - pid * p.splits;
+  const int k_begin = split * p.k_per_split;
+  const int k_end = min(p.K, k_begin + p.k_per_split);
   const int per_group = SG_GROUP_M * p.tiles_n;
   const int group = pid / per_group;
   const int first_m = group * SG_GROUP_M;
@@ -97,10 +106,10 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
       } else {
         float t[4];
 #pragma unroll
-        for (int c = 0; c < 4; c++) t[c] = (m < p.M && k + c < p.K) ? p.A[(size_t)m * p.lda + k + c] : 0.f;
+        for (int c = 0; c < 4; c++) t[c] = (m < p.M && k + c < k_end) ? p.A[(size_t)m * p.lda + k + c] : 0.f;
         ra[i] = make_float4(t[0], t[1], t[2], t[3]);
 #pragma unroll
-        for (int c = 0; c < 4; c++) t[c] = (kb < p.K && n + c < p.N) ? p.B[(size_t)kb * p.ldb + n + c] : 0.f;
+        for (int c = 0; c < 4; c++) t[c] = (kb < k_end && n + c < p.N) ? p.B[(size_t)kb * p.ldb + n + c] : 0.f;
         rb[i] = make_float4(t[0], t[1], t[2], t[3]);
       }
     }
@@ -129,8 +138,8 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc2[i][j] = make_float2(0.f, 0.f);
 
-  const int KT = (p.K + SG_BK - 1) / SG_BK;
-  gload(0, 0);
+  const int KT = (max(k_end - k_begin, 0) + SG_BK - 1) / SG_BK;
+  gload(k_begin, 0);
   sstore(0);
   __syncthreads();
 
@@ -150,7 +159,7 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   for (int kt = 0; kt < KT; kt++) {
     const int buf = kt & 1;
     const bool more = kt + 1 < KT;
-    if (more) gload((kt + 1) * SG_BK, buf ^ 1);
+    if (more) gload(k_begin + (kt + 1) * SG_BK, buf ^ 1);
     lfrag(buf, 0, 0);
 #pragma unroll
     for (int k = 0; k < SG_BK; k++) {
@@ -171,6 +180,41 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   for (int ip = 0; ip < 4; ip++)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc[2 * ip][j] = acc2[ip][j].x, acc[2 * ip + 1][j] = acc2[ip][j].y;
+
+  if (p.splits > 1) {
+    // park this split's accumulators (coalesced: float4 f of every thread is contiguous across the CTA)
+    float4 *mine = p.scratch + ((size_t)pid * p.splits + split) * (16 * SG_THREADS);
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+      for (int h = 0; h < 2; h++)
+        __stcg(mine + (i * 2 + h) * SG_THREADS + tid,
+               make_float4(acc[i][h * 4 + 0], acc[i][h * 4 + 1], acc[i][h * 4 + 2], acc[i][h * 4 + 3]));
+    __shared__ bool last_split;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) last_split = (atomicAdd(p.tickets + pid, 1u) == (unsigned int)p.splits - 1);
+    __syncthreads();
+    if (!last_split) return;
+    __threadfence();
+    // the last CTA of the tile adds all splits in index order (its own included): a fixed order
+    const float4 *all = p.scratch + (size_t)pid * p.splits * (16 * SG_THREADS);
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+    for (int sp = 0; sp < p.splits; sp++) {
+      const float4 *src = all + (size_t)sp * (16 * SG_THREADS);
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const float4 v = __ldcg(src + (i * 2 + h) * SG_THREADS + tid);
+          acc[i][h * 4 + 0] += v.x, acc[i][h * 4 + 1] += v.y, acc[i][h * 4 + 2] += v.z, acc[i][h * 4 + 3] += v.w;
+        }
+    }
+    if (tid == 0) p.tickets[pid] = 0;  // at rest for the next launch
+  }
 
   // epilogue
 #pragma unroll
@@ -232,8 +276,39 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
   const bool fast = (M % SG_BM == 0) && (N % SG_BN == 0) && (K % SG_BK == 0) && K > 0 &&
                     (lda % 4 == 0) && (ldb % 4 == 0) && (ldc % 4 == 0) &&
                     ((((uintptr_t)A | (uintptr_t)B | (uintptr_t)C) & 15) == 0);
-  const unsigned int grid = (unsigned int)(p.tiles_m * p.tiles_n);
+  const int tiles = p.tiles_m * p.tiles_n;
   cudaStream_t st = (cudaStream_t)stream;
+  // split-K when the tiles alone would leave most of the GPU idle (room: 2 CTAs per SM) -- the
+  // 64 x 4096 x 64 case of cuda/gemm_fp32.cu:162-258,714-718 and cux's demo shape
+  p.splits = 1, p.k_per_split = K > 0 ? K : 1, p.scratch = nullptr, p.tickets = nullptr;
+  const int room = 2 * ctx->sm_count;
+  if (tiles * 2 <= room && K >= 256) {
+    int splits = room / tiles;
+    const int max_by_k = K / 64;  // at least 64 k per split
+    if (splits > max_by_k) splits = max_by_k;
+    if (splits > 64) splits = 64;
+    if (splits > 1) {
+      int kps = (K + splits - 1) / splits;
+      kps = (kps + SG_BK - 1) / SG_BK * SG_BK;
+      splits = (K + kps - 1) / kps;
+      // layout: [0, 1024) per-tile tickets (tiles <= 148 here; zero at rest), then the parked accumulators
+      const size_t need = 1024 + (size_t)tiles * splits * 16 * SG_THREADS * sizeof(float4);
+      if (ctx->sg_scratch_bytes < need) {
+        if (ctx->sg_scratch) {
+          CUXB_CUDA(cudaDeviceSynchronize());
+          CUXB_CUDA(cudaFree(ctx->sg_scratch));
+          ctx->sg_scratch = nullptr, ctx->sg_scratch_bytes = 0;
+        }
+        CUXB_CUDA(cudaMalloc(&ctx->sg_scratch, need));
+        CUXB_CUDA(cudaMemset(ctx->sg_scratch, 0, 1024));
+        ctx->sg_scratch_bytes = need;
+      }
+      p.splits = splits, p.k_per_split = kps;
+      p.tickets = (unsigned int *)ctx->sg_scratch;
+      p.scratch = (float4 *)((char *)ctx->sg_scratch + 1024);
+    }
+  }
+  const unsigned int grid = (unsigned int)(tiles * p.splits);
   if (fast)
     sgemm_kernel<true><<<grid, SG_THREADS, 0, st>>>(p);
   else

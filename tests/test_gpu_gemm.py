@@ -390,3 +390,20 @@ def test_two_scans_on_two_streams_do_not_deadlock():
     torch.cuda.synchronize()
     assert np.array_equal(host(o1), oracle.scan_i32(x, 1)) and np.array_equal(host(o2), oracle.scan_i32(x, 2))
     c2.close()
+
+
+@pytest.mark.parametrize("shape", [(64, 64, 4096), (512, 576, 480), (128, 128, 8192), (100, 70, 1033), (256, 256, 256)])
+def test_sgemm_split_k_shapes(shape):
+    # few tiles, long K: the kernel splits K across CTAs and the last CTA of a tile adds the splits in a
+    # fixed order (cuda/gemm_fp32.cu:162-258 is the reference's atomicAdd split-K study; 64x4096x64 is its case)
+    M, N, K = shape
+    A, B, C = dg.int_fill((M, K), -2, 5, tag=87), dg.int_fill((K, N), -2, 5, tag=88), dg.int_fill((M, N), -2, 5, tag=89)
+    for ab in ((1.0, 3.0), (1.0, 0.0)):
+        want = oracle.gemm_f32(A, B, C, *ab, order="ikj", threads=8)
+        for _ in range(2):  # twice: tickets must be back at rest
+            assert np.array_equal(bits32(run_sgemm(A, B, C, *ab)), bits32(want))
+    Af, Bf = dg.uniform_fill((M, K), tag=90), dg.uniform_fill((K, N), tag=91)
+    got = run_sgemm(Af, Bf, C, 1.0, 0.0)
+    want = oracle.gemm_f32(Af, Bf, C, 1.0, 0.0, order="ikj", threads=8)
+    assert np.max(np.abs(got - want)) <= 2 * K * EPS
+    assert np.array_equal(got, run_sgemm(Af, Bf, C, 1.0, 0.0))  # deterministic: same bits every run
