@@ -49,7 +49,7 @@ struct SgemmArgs {
   unsigned int *tickets;  // [tile], zero at rest
 };
 
-template <bool FAST>
+template <bool FAST, bool SPLITK>
 __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p) {
   __shared__ __align__(16) float As[2][SG_BK][SG_LDA];
   __shared__ __align__(16) float Bs[2][SG_BK][SG_BN];
@@ -67,10 +67,10 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   const int tn0 = warp_n * 32 + lane_n * 4;
 
   // grouped rasterisation
-  const int pid = blockIdx.x / p.splits;
-  const int split = blockIdx.x - pid * p.splits;
-  const int k_begin = split * p.k_per_split;
-  const int k_end = min(p.K, k_begin + p.k_per_split);
+  const int pid = SPLITK ? blockIdx.x / p.splits : blockIdx.x;
+  const int split = SPLITK ? blockIdx.x - pid * p.splits : 0;
+  const int k_begin = SPLITK ? split * p.k_per_split : 0;
+  const int k_end = SPLITK ? min(p.K, k_begin + p.k_per_split) : p.K;
   const int per_group = SG_GROUP_M * p.tiles_n;
   const int group = pid / per_group;
   const int first_m = group * SG_GROUP_M;
@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc[2 * ip][j] = acc2[ip][j].x, acc[2 * ip + 1][j] = acc2[ip][j].y;
 
-  if (p.splits > 1) {
+  if (SPLITK) {
     // park this split's accumulators (coalesced: float4 f of every thread is contiguous across the CTA)
     float4 *mine = p.scratch + ((size_t)pid * p.splits + split) * (16 * SG_THREADS);
 #pragma unroll
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   }
 }
 
-const void *sgemm_kernel_symbol() { return (const void *)sgemm_kernel<true>; }
+const void *sgemm_kernel_symbol() { return (const void *)sgemm_kernel<true, false>; }
 
 }  // namespace cuxb
 
@@ -309,10 +309,13 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
     }
   }
   const unsigned int grid = (unsigned int)(tiles * p.splits);
-  if (fast)
-    sgemm_kernel<true><<<grid, SG_THREADS, 0, st>>>(p);
-  else
-    sgemm_kernel<false><<<grid, SG_THREADS, 0, st>>>(p);
+  if (p.splits > 1) {
+    if (fast) sgemm_kernel<true, true><<<grid, SG_THREADS, 0, st>>>(p);
+    else sgemm_kernel<false, true><<<grid, SG_THREADS, 0, st>>>(p);
+  } else {
+    if (fast) sgemm_kernel<true, false><<<grid, SG_THREADS, 0, st>>>(p);
+    else sgemm_kernel<false, false><<<grid, SG_THREADS, 0, st>>>(p);
+  }
   CUXB_LAUNCHED();
   return 0;
 }
