@@ -72,6 +72,7 @@ SIGNATURES = {
     "cuxb_linear_bf16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i], _i),
     "cuxb_linear_f16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _i], _i),
     "cuxb_convert": ([_vp, _vp, _ll, _vp, _i, _vp, _i], _i),
+    "cuxb_fill_random": ([_vp, _vp, _ll, _vp, _i, _i, _i, _i, C.c_ulonglong], _i),
     "cuxb_dot_f32_host": ([_vp, _ll, _vp, _vp, _vp], _i),
     "cuxb_sum_f32_host": ([_vp, _ll, _vp, _vp], _i),
     "cuxb_nrm2_f32_host": ([_vp, _ll, _vp, _vp], _i),
@@ -206,6 +207,9 @@ class Context:
 
     def convert(self, n, src, src_dtype, dst, dst_dtype, stream=0):
         check(lib().cuxb_convert(self._h, stream, n, src, src_dtype, dst, dst_dtype), "cuxb_convert")
+
+    def fill_random(self, n, dst, dtype, lo, hi, decimal_pose=0, seed=20240607, stream=0):
+        check(lib().cuxb_fill_random(self._h, stream, n, dst, dtype, lo, hi, decimal_pose, seed), "cuxb_fill_random")
 
     def occupancy(self, kernel):
         ab, occ, th, sm = _i(), C.c_double(), _i(), _i()

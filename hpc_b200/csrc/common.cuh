@@ -87,7 +87,8 @@ struct cuxb_ctx {
   cuxb::TmaCacheEntry tma_cache[16];  // most recent TMA descriptors (encoding one costs microseconds)
   int tma_cache_n;
   int tma_cache_next;
-  std::mutex *mu;
+  std::mutex *mu;      // serialises the *_host entry points (they share the staging buffers)
+  std::mutex *tma_mu;  // guards the descriptor cache (taken inside kernels' entry points, never with mu's order reversed)
 };
 
 namespace cuxb {

@@ -68,6 +68,7 @@ CUXB_API int cuxb_ctx_create(int device, cuxb_ctx **out) {
   c->cc_major = prop.major;
   c->cc_minor = prop.minor;
   c->mu = new std::mutex();
+  c->tma_mu = new std::mutex();
   cudaError_t e;
   e = cudaMalloc(&c->red_partials, kReduceMaxBlocks * 8);
   if (e == cudaSuccess) e = cudaMalloc((void **)&c->red_ticket, 256);
@@ -99,6 +100,7 @@ CUXB_API int cuxb_ctx_destroy(cuxb_ctx *c) {
     if (c->stage[i]) cudaFree(c->stage[i]);
   if (c->stage_stream) cudaStreamDestroy(c->stage_stream);
   delete c->mu;
+  delete c->tma_mu;
   delete c;
   return 0;
 }

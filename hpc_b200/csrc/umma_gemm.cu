@@ -544,7 +544,7 @@ static int make_map(cuxb_ctx *ctx, CUtensorMap *map, const void *base, int ebyte
                     bool swizzle128 = true) {
   static_assert(sizeof(CUtensorMap) == 128, "descriptor size");
   {
-    std::lock_guard<std::mutex> g(*ctx->mu);
+    std::lock_guard<std::mutex> g(*ctx->tma_mu);
     for (int i = 0; i < ctx->tma_cache_n; i++) {
       const TmaCacheEntry &e = ctx->tma_cache[i];
       if (e.base == base && e.rows == rows && e.cols == cols && e.ld == ld && e.box_cols == box_cols &&
@@ -566,7 +566,7 @@ static int make_map(cuxb_ctx *ctx, CUtensorMap *map, const void *base, int ebyte
   CUXB_REQUIRE(r == CUDA_SUCCESS, CUXB_ERR_INVALID,
                "cuTensorMapEncodeTiled failed (%d): base=%p rows=%llu cols=%llu ld=%llu box=%ux%u", (int)r, base,
                (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, box_cols, box_rows);
-  std::lock_guard<std::mutex> g(*ctx->mu);
+  std::lock_guard<std::mutex> g(*ctx->tma_mu);
   TmaCacheEntry &e = ctx->tma_cache[ctx->tma_cache_next];
   e.base = base, e.rows = rows, e.cols = cols, e.ld = ld, e.box_cols = box_cols, e.box_rows = box_rows, e.dtype = (int)dt * 2 + (swizzle128 ? 1 : 0);
   memcpy(e.map, map, sizeof(CUtensorMap));

@@ -6,7 +6,7 @@
 // added through the OpFactory.  Unlike the reference it returns a status: non-zero if any check
 // failed, and it also compares host kernel 0 with device kernel 0 (the reference never does).
 //
-//   cux_demo [--len N] [--quick]
+//   cux_demo [--len N] [--quick] [--device-fill] [--pinned]
 #include <cstring>
 #include <memory>
 
@@ -18,6 +18,12 @@ extern cux::KernelInterface *GemmGPUPlugin();
 namespace {
 
 int g_failures = 0;
+bool g_device_fill = false;  // --device-fill: BindAndFillOnDevice instead of BindAndFill
+
+void Bind(cux::Executor &ex, const std::vector<cux::Array4D *> &in, const std::vector<cux::Array4D *> &out, int lo, int hi) {
+  if (g_device_fill) ex.BindAndFillOnDevice(in, out, lo, hi, 0);
+  else ex.BindAndFill(in, out, lo, hi, 0);
+}
 
 template <typename T> std::vector<T> Snapshot(cux::Array4D *a) {
   T *p = a->GetCpuData<T>(cux::NO_PUSH);
@@ -43,7 +49,7 @@ void DotProductTest(int data_len) {
   ex.SelectOp("dot", "");
   ex.AddPlugin(DotProductGPUPlugin(), cux::OpRunMode::ON_DEVICE);
   cux::Array4D in_a(1, 1, 1, data_len), in_b(1, 1, 1, data_len), out(1, 1, 1, 1);
-  ex.BindAndFill({&in_a, &in_b}, {&out}, -2, 2, 0);
+  Bind(ex, {&in_a, &in_b}, {&out}, -2, 2);
   ex.Run(cux::OpRunMode::ON_HOST);
   auto host = Snapshot<float>(&out);
   ex.Run(cux::OpRunMode::ON_DEVICE);
@@ -56,7 +62,7 @@ void Nrm2Test(int data_len) {
   ex.Initialize(0);
   ex.SelectOp("nrm2", "");
   cux::Array4D in(1, 1, 1, data_len), out(1, 1, 1, 1);
-  ex.BindAndFill({&in}, {&out}, -1, 1, 0);
+  Bind(ex, {&in}, {&out}, -1, 1);
   ex.Run(cux::OpRunMode::ON_HOST);
   auto host = Snapshot<float>(&out);
   ex.Run(cux::OpRunMode::ON_DEVICE);
@@ -69,7 +75,7 @@ void ReduceSumTest(int data_len) {
   ex.Initialize(0);
   ex.SelectOp("reduce_sum", "");
   cux::Array4D in(1, 1, 1, data_len), out(1, 1, 1, 1);
-  ex.BindAndFill({&in}, {&out}, -2, 2, 0);
+  Bind(ex, {&in}, {&out}, -2, 2);
   ex.Run(cux::OpRunMode::ON_HOST);
   auto host = Snapshot<float>(&out);
   ex.Run(cux::OpRunMode::ON_DEVICE);
@@ -84,7 +90,7 @@ void GEMMTest(int block_size) {
   ex.AddPlugin(GemmGPUPlugin(), cux::OpRunMode::ON_DEVICE);
   cux::Array4D in_a(1, 1, block_size * 16, block_size * 15), in_b(1, 1, block_size * 15, block_size * 18);
   cux::Array4D out_c(1, 1, in_a.shape()[cux::HEIGHT], in_b.shape()[cux::WIDTH]);
-  ex.BindAndFill({&in_a, &in_b}, {&out_c}, -2, 5, 0);
+  Bind(ex, {&in_a, &in_b}, {&out_c}, -2, 5);
   ex.Run(cux::OpRunMode::ON_HOST);
   auto host = Snapshot<float>(&out_c);
   out_c.Restore(cux::TypeFlag::FLOAT32, cux::ON_HOST);  // beta: the device run must start from the original C
@@ -100,7 +106,7 @@ void LinearInt8Test(int M, int N, int K) {
   ex.Initialize(0);
   ex.SelectOp("linear_int8", "");
   cux::Array4D a(1, 1, M, K), bt(1, 1, N, K), c(1, 1, M, N);
-  ex.BindAndFill({&a, &bt}, {&c}, -8, 8, 0);
+  Bind(ex, {&a, &bt}, {&c}, -8, 8);
   ex.Run(cux::OpRunMode::ON_HOST);
   auto host = Snapshot<int32_t>(&c);
   ex.Run(cux::OpRunMode::ON_DEVICE);
@@ -113,7 +119,7 @@ void ScanTest(int n) {
   ex.Initialize(0);
   ex.SelectOp("scan_i32", "");
   cux::Array4D in(1, 1, 1, n), out(1, 1, 1, n);
-  ex.BindAndFill({&in}, {&out}, -2, 2, 0);
+  Bind(ex, {&in}, {&out}, -2, 2);
   ex.Run(cux::OpRunMode::ON_HOST);
   auto host = Snapshot<int32_t>(&out);
   ex.Run(cux::OpRunMode::ON_DEVICE);
@@ -129,6 +135,8 @@ int main(int argc, char **argv) {
   for (int i = 1; i < argc; i++) {
     if (!std::strcmp(argv[i], "--len") && i + 1 < argc) data_len = std::atoi(argv[++i]);
     else if (!std::strcmp(argv[i], "--quick")) { data_len = 409600; gemm_block = 8; }
+    else if (!std::strcmp(argv[i], "--device-fill")) g_device_fill = true;
+    else if (!std::strcmp(argv[i], "--pinned")) cux::Array4D::UsePinnedHostMemory(true);
   }
   cux::InitEnvironment();
   cux::QueryDevices();

@@ -30,8 +30,15 @@ public:
     return static_cast<DType *>(FetchGpu(DataType<DType>::kFlag, mode));
   }
 
-  // decimal_pose: 0 for integers, 1 for x.x, 2 for x.xx ... (host only, like array.cpp:46-60)
+  // decimal_pose: 0 for integers, 1 for x.x, 2 for x.xx ...  ON_HOST is the reference's path
+  // (array.cpp:46-60).  ON_DEVICE -- rejected by the reference -- fills the device copy with
+  // cuxb_fill_random (needs SetDeviceContext); the host copy is pulled lazily by GetCpuData(PUSH...).
   void Fill(int min_value, int max_value, int decimal_pose, int type_flag, OpRunMode mode = OpRunMode::ON_HOST);
+  // Context used by the device-side extensions (Fill ON_DEVICE).  Borrowed, not owned.
+  static void SetDeviceContext(cuxb_ctx *ctx) { DeviceContext() = ctx; }
+  // Allocate host copies as pinned memory (cuxb_malloc_host): H2D / D2H then run as DMA at PCIe speed.
+  // Off by default so that host-only use needs no GPU.
+  static void UsePinnedHostMemory(bool on) { Pinned() = on; }
   void Save(int type_flag, OpRunMode mode, bool is_save_if_empty = true);
   void Restore(int type_flag, OpRunMode mode);
 
@@ -49,12 +56,17 @@ public:
   void PrecsGpuCvt(cuxb_ctx *ctx, int src_type_flag, int dst_type_flag);
 
 private:
+  static cuxb_ctx *&DeviceContext() { static cuxb_ctx *c = nullptr; return c; }
+  static bool &Pinned() { static bool p = false; return p; }
+  void *HostAlloc(size_t bytes);
+  void HostFree(void *p);
   void *FetchCpu(int type_flag, DataFetchMode mode);
   void *FetchGpu(int type_flag, DataFetchMode mode);
 
   std::vector<int> shape_;
   int num_element_;
   std::vector<void *> cpu_, gpu_;          // indexed by TypeFlag
+  std::vector<bool> cpu_pinned_;
   std::vector<void *> cpu_backup_, gpu_backup_;
 };
 

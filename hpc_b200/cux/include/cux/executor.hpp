@@ -20,6 +20,11 @@ public:
   void AddPlugin(KernelInterface *kernel_if, OpRunMode mode);
   void BindAndFill(const std::vector<Array4D *> &inputs, const std::vector<Array4D *> &outputs, int min_value,
                    int max_value, int decimal_pose);
+  // Extension: the same, but filled and converted on the GPU (cuxb_fill_random + cuxb_convert) -- at the
+  // BASELINE sizes (16384^2 matrices) the reference's host fill and scalar conversion loops take seconds
+  // per array.  Host copies appear lazily when a host kernel asks for them (GetCpuData(PUSH_IF_EMPTY)).
+  void BindAndFillOnDevice(const std::vector<Array4D *> &inputs, const std::vector<Array4D *> &outputs, int min_value,
+                           int max_value, int decimal_pose);
   void Run(const OpRunMode mode);
 
   // Additions (the reference only prints its verdicts, op_assistor.h:59-69):

@@ -7,11 +7,13 @@ namespace cux {
 Array4D::Array4D(int num, int channels, int height, int width)
     : shape_{num, channels, height, width},
       num_element_(num * channels * height * width),
-      cpu_(TYPES_NUM, nullptr), gpu_(TYPES_NUM, nullptr), cpu_backup_(TYPES_NUM, nullptr), gpu_backup_(TYPES_NUM, nullptr) {}
+      cpu_(TYPES_NUM, nullptr), gpu_(TYPES_NUM, nullptr), cpu_pinned_(TYPES_NUM, false),
+      cpu_backup_(TYPES_NUM, nullptr), gpu_backup_(TYPES_NUM, nullptr) {}
 
 Array4D::~Array4D() {
   for (int t = 0; t < TYPES_NUM; t++) {
-    std::free(cpu_[t]);
+    if (cpu_pinned_[t]) cuxb_free_host(cpu_[t]);
+    else std::free(cpu_[t]);
     std::free(cpu_backup_[t]);
     if (gpu_[t]) cuxb_free(gpu_[t]);
     if (gpu_backup_[t]) cuxb_free(gpu_backup_[t]);
@@ -22,7 +24,12 @@ void *Array4D::FetchCpu(int t, DataFetchMode mode) {
   const size_t bytes = (size_t)num_element_ * TypeSize(t);
   bool created = false;
   if (cpu_[t] == nullptr) {
-    cpu_[t] = std::malloc(bytes ? bytes : 1);
+    if (Pinned()) {
+      CUXB_CHECK(cuxb_malloc_host(&cpu_[t], bytes));
+      cpu_pinned_[t] = true;
+    } else {
+      cpu_[t] = std::malloc(bytes ? bytes : 1);
+    }
     if (cpu_[t] == nullptr) CUXLOG_ERR("Array4D: out of host memory (%zu bytes).", bytes);
     created = true;
   }
@@ -45,7 +52,19 @@ void *Array4D::FetchGpu(int t, DataFetchMode mode) {
 }
 
 void Array4D::Fill(int min_value, int max_value, int decimal_pose, int type_flag, OpRunMode mode) {
-  if (mode == OpRunMode::ON_DEVICE) CUXLOG_ERR("Fill Array ON_DEVICE does not supported for now.");
+  if (mode == OpRunMode::ON_DEVICE) {
+    if (DeviceContext() == nullptr) CUXLOG_ERR("Fill Array ON_DEVICE needs Array4D::SetDeviceContext first.");
+    void *d = FetchGpu(type_flag, NO_PUSH);
+    static unsigned long long call = 0;  // a different stream of values for every array, reproducible run to run
+    const unsigned long long seed = DataFiller::Seed() + 0x51ED270B27B4F3CFull * (++call);
+    if (min_value == max_value)  // constant fill: the random fill of a one-value range
+      CUXB_CHECK(cuxb_fill_random(DeviceContext(), nullptr, num_element_, d, type_flag, min_value, max_value, 0, seed));
+    else
+      CUXB_CHECK(cuxb_fill_random(DeviceContext(), nullptr, num_element_, d, type_flag, min_value, max_value, decimal_pose, seed));
+    if (cpu_[type_flag] != nullptr)  // keep an existing host copy coherent
+      CUXB_CHECK(cuxb_memcpy_d2h(cpu_[type_flag], d, (size_t)num_element_ * TypeSize(type_flag), nullptr));
+    return;
+  }
   TYPE_SWITCH(type_flag, T, {
     T *p = GetCpuData<T>();
     if (min_value == max_value)

@@ -96,6 +96,24 @@ void Executor::BindAndFill(const std::vector<Array4D *> &inputs, const std::vect
   }
 }
 
+void Executor::BindAndFillOnDevice(const std::vector<Array4D *> &inputs, const std::vector<Array4D *> &outputs,
+                                   int min_value, int max_value, int decimal_pose) {
+  if (op_ == nullptr) CUXLOG_ERR("The operator has not been selected yet. Please select an operator first.");
+  inputs_ = inputs;
+  outputs_ = outputs;
+  Array4D::SetDeviceContext(op_assistor_->ctx());
+  std::vector<int> used;
+  op_->ExtractDataTypes(used);
+  auto prepare = [&](Array4D *a) {
+    a->Fill(min_value, max_value, decimal_pose, TypeFlag::FLOAT32, OpRunMode::ON_DEVICE);
+    for (int t = 0; t < (int)used.size(); t++)
+      if (t != TypeFlag::FLOAT32 && used[t]) a->PrecsGpuCvt(op_assistor_->ctx(), TypeFlag::FLOAT32, t);
+  };
+  for (Array4D *a : inputs_) prepare(a);
+  for (Array4D *a : outputs_) prepare(a);
+  CUXB_CHECK(cuxb_device_sync());
+}
+
 void Executor::Run(const OpRunMode mode) {
   if (op_ == nullptr) CUXLOG_ERR("The operator has not been selected yet. Please select an operator first.");
   if (mode == OpRunMode::ON_HOST) op_->RunOnHost(inputs_, outputs_);

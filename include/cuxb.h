@@ -206,6 +206,13 @@ int cuxb_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, con
  * (round to nearest even) and back. */
 int cuxb_convert(cuxb_ctx *ctx, void *stream, long long n, const void *src, int src_dtype, void *dst,
                  int dst_dtype);
+/* Random fill on the device with the distribution of DataFiller::RandomFill
+ * (0-frameworks/cux/include/util/data_filler.h:41-60): integers in [min_value, max_value], or, with
+ * decimal_pose > 0, [min_value, max_value) plus that many random decimal digits.  Element i is a pure
+ * function of (seed, i).  Backs Array4D::Fill(..., ON_DEVICE), which the reference does not implement
+ * (src/array.cpp:47-49). */
+int cuxb_fill_random(cuxb_ctx *ctx, void *stream, long long n, void *dst, int dtype, int min_value, int max_value,
+                     int decimal_pose, unsigned long long seed);
 
 /* ---- host-buffer entry points: what a cux plugin that is handed HOST arrays
  * calls.  Inputs are copied host->device, the kernel runs, the result is

@@ -34,3 +34,10 @@ def test_demo_reference_shapes():
 def test_demo_quick():
     r = run_demo("--quick")
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+def test_demo_with_device_side_fill_and_pinned_host_memory():
+    # Executor::BindAndFillOnDevice (fill + dtype conversion on the GPU) and pinned Array4D host copies
+    r = run_demo("--quick", "--device-fill", "--pinned")
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "cux_demo: all checks passed" in r.stdout and "Fail" not in r.stdout

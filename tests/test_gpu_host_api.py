@@ -98,3 +98,34 @@ def test_occupancy_hook_and_launch_counter():
     assert capi.launch_count() == before + 1 and float(out[0]) == 1000.0
     with pytest.raises(capi.CuxbError):
         c.occupancy("nope")
+
+
+def _splitmix64(x):
+    x = (x + np.uint64(0x9E3779B97F4A7C15))
+    x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return x ^ (x >> np.uint64(31))
+
+
+def test_device_random_fill_is_a_pure_function_of_seed_and_index():
+    c = ctx()
+    n, lo, hi, seed = 1_000_003, -2, 5, 12345
+    d = torch.empty(n, dtype=torch.float32, device="cuda")
+    c.fill_random(n, d.data_ptr(), capi.FLOAT32, lo, hi, 0, seed)
+    sync()
+    got = host(d)
+    with np.errstate(over="ignore"):
+        h = _splitmix64(np.uint64(seed) + np.arange(n, dtype=np.uint64) * np.uint64(0xD1342543DE82EF95))
+    want = (lo + ((h >> np.uint64(32)) % np.uint64(hi - lo + 1)).astype(np.int64)).astype(np.float32)
+    assert np.array_equal(got, want)
+    assert got.min() == lo and got.max() == hi and set(np.unique(got)) == set(range(lo, hi + 1))
+    # other element types get the same integers; decimals stay inside [lo, hi)
+    for dt, tdt in ((capi.INT32, torch.int32), (capi.INT8, torch.int8), (capi.FLOAT16, torch.float16)):
+        t = torch.empty(n, dtype=tdt, device="cuda")
+        c.fill_random(n, t.data_ptr(), dt, lo, hi, 0, seed)
+        sync()
+        assert np.array_equal(t.float().cpu().numpy(), want)
+    c.fill_random(n, d.data_ptr(), capi.FLOAT32, 0, 3, 2, seed)
+    sync()
+    g = host(d)
+    assert g.min() >= 0 and g.max() < 3 and np.allclose(g * 100, np.round(g * 100), atol=1e-3)
