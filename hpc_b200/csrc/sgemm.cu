@@ -281,32 +281,43 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
   // split-K when the tiles alone would leave most of the GPU idle (room: 2 CTAs per SM) -- the
   // 64 x 4096 x 64 case of cuda/gemm_fp32.cu:162-258,714-718 and cux's demo shape
   p.splits = 1, p.k_per_split = K > 0 ? K : 1, p.scratch = nullptr, p.tickets = nullptr;
-  const int room = 2 * ctx->sm_count;
-  if (tiles * 2 <= room && K >= 256) {
-    int splits = room / tiles;
-    const int max_by_k = K / 64;  // at least 64 k per split
-    if (splits > max_by_k) splits = max_by_k;
-    if (splits > 64) splits = 64;
-    if (splits > 1) {
-      int kps = (K + splits - 1) / splits;
-      kps = (kps + SG_BK - 1) / SG_BK * SG_BK;
-      splits = (K + kps - 1) / kps;
-      // layout: [0, 1024) per-tile tickets (tiles <= 148 here; zero at rest), then the parked accumulators
-      const size_t need = 1024 + (size_t)tiles * splits * 16 * SG_THREADS * sizeof(float4);
-      if (ctx->sg_scratch_bytes < need) {
-        if (ctx->sg_scratch) {
-          CUXB_CUDA(cudaDeviceSynchronize());
-          CUXB_CUDA(cudaFree(ctx->sg_scratch));
-          ctx->sg_scratch = nullptr, ctx->sg_scratch_bytes = 0;
-        }
-        CUXB_CUDA(cudaMalloc(&ctx->sg_scratch, need));
-        CUXB_CUDA(cudaMemset(ctx->sg_scratch, 0, 1024));
-        ctx->sg_scratch_bytes = need;
+  const int room = 2 * ctx->sm_count;  // CTAs resident at once
+  int splits = 1;
+  if (tiles <= 1024 && K >= 256) {
+    // pick the split count whose last wave is fullest (efficiency = work / (waves * room)); splitting
+    // costs one round trip of the accumulators through L2, so it has to buy at least 8 %
+    auto eff = [&](int sp) {
+      const int ctas = tiles * sp;
+      const int waves = (ctas + room - 1) / room;
+      return (double)ctas / ((double)waves * room);
+    };
+    double best = eff(1) * 1.08;
+    const int max_sp = K / 64 < 32 ? K / 64 : 32;  // at least 64 k per split
+    for (int sp = 2; sp <= max_sp && tiles * sp <= 1024; sp++)
+      if (eff(sp) > best) best = eff(sp), splits = sp;
+  }
+  if (splits > 1) {
+    int kps = (K + splits - 1) / splits;
+    kps = (kps + SG_BK - 1) / SG_BK * SG_BK;
+    splits = (K + kps - 1) / kps;
+  }
+  if (splits > 1) {
+    // layout: [0, 4096) per-tile tickets (tiles <= 1024; zero at rest), then the parked accumulators
+    const size_t need = 4096 + (size_t)tiles * splits * 16 * SG_THREADS * sizeof(float4);
+    if (ctx->sg_scratch_bytes < need) {
+      if (ctx->sg_scratch) {
+        CUXB_CUDA(cudaDeviceSynchronize());
+        CUXB_CUDA(cudaFree(ctx->sg_scratch));
+        ctx->sg_scratch = nullptr, ctx->sg_scratch_bytes = 0;
       }
-      p.splits = splits, p.k_per_split = kps;
-      p.tickets = (unsigned int *)ctx->sg_scratch;
-      p.scratch = (float4 *)((char *)ctx->sg_scratch + 1024);
+      CUXB_CUDA(cudaMalloc(&ctx->sg_scratch, need));
+      CUXB_CUDA(cudaMemset(ctx->sg_scratch, 0, 4096));
+      ctx->sg_scratch_bytes = need;
     }
+    p.splits = splits, p.k_per_split = (K + splits - 1) / splits;
+    p.k_per_split = (p.k_per_split + SG_BK - 1) / SG_BK * SG_BK;
+    p.tickets = (unsigned int *)ctx->sg_scratch;
+    p.scratch = (float4 *)((char *)ctx->sg_scratch + 4096);
   }
   const unsigned int grid = (unsigned int)(tiles * p.splits);
   if (p.splits > 1) {

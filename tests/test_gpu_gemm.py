@@ -392,7 +392,7 @@ def test_two_scans_on_two_streams_do_not_deadlock():
     c2.close()
 
 
-@pytest.mark.parametrize("shape", [(64, 64, 4096), (512, 576, 480), (128, 128, 8192), (100, 70, 1033), (256, 256, 256)])
+@pytest.mark.parametrize("shape", [(64, 64, 4096), (512, 576, 480), (128, 128, 8192), (100, 70, 1033), (256, 256, 256), (1280, 2048, 4096)])
 def test_sgemm_split_k_shapes(shape):
     # few tiles, long K: the kernel splits K across CTAs and the last CTA of a tile adds the splits in a
     # fixed order (cuda/gemm_fp32.cu:162-258 is the reference's atomicAdd split-K study; 64x4096x64 is its case)
