@@ -12,11 +12,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def run_demo(*args):
-    from hpc_b200 import build as b
-    from hpc_b200.cux import build as hb
-    b.build(verbose=False)
-    _, demo, _ = hb.build()
-    return subprocess.run([demo, *args], capture_output=True, text=True, timeout=600)
+    # use the binaries built by __graft_entry__.build(); never rebuild libcuxb.so here -- this process
+    # has it loaded (other tests), and replacing a mapped library under a running process is unsafe
+    demo = os.path.join(ROOT, "hpc_b200", "cux", "cux_demo")
+    if not os.path.exists(demo):
+        from hpc_b200.cux import build as hb
+        _, demo, _ = hb.build()
+    return subprocess.run([demo, *args], capture_output=True, text=True, timeout=250)
 
 
 def test_demo_reference_shapes():
