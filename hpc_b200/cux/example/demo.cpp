@@ -6,7 +6,13 @@
 // added through the OpFactory.  Unlike the reference it returns a status: non-zero if any check
 // failed, and it also compares host kernel 0 with device kernel 0 (the reference never does).
 //
-//   cux_demo [--len N] [--quick] [--device-fill] [--pinned]
+//   cux_demo [--len N] [--quick] [--device-fill] [--pinned] [--device-only] [--gemm-block B]
+//            [--linear M N K] [--scan-len N]
+//   BASELINE sizes through the cux harness:
+//   cux_demo --device-only --device-fill --len 268435456 --gemm-block 512 --gemm-range -1 1 \\
+//            --linear 8192 8192 8192 --scan-len 1073741824
+//   (--gemm-range -1 1: with K = 7680 the reference's [-2,5] fill makes |C| ~ 17000, which fp16 storage
+//    cannot hold exactly, so the fp16 kernel would fail cux's 1e-3 mean-error rule against the fp32 one)
 #include <cstring>
 #include <memory>
 
@@ -19,6 +25,9 @@ namespace {
 
 int g_failures = 0;
 bool g_device_fill = false;  // --device-fill: BindAndFillOnDevice instead of BindAndFill
+bool g_device_only = false;  // --device-only: skip the host kernels (config-sized problems: the naive
+                             // host GEMM alone would run for hours); device kernels are still checked
+                             // against device kernel 0 by the ResultChecker
 
 void Bind(cux::Executor &ex, const std::vector<cux::Array4D *> &in, const std::vector<cux::Array4D *> &out, int lo, int hi) {
   if (g_device_fill) ex.BindAndFillOnDevice(in, out, lo, hi, 0);
@@ -50,10 +59,10 @@ void DotProductTest(int data_len) {
   ex.AddPlugin(DotProductGPUPlugin(), cux::OpRunMode::ON_DEVICE);
   cux::Array4D in_a(1, 1, 1, data_len), in_b(1, 1, 1, data_len), out(1, 1, 1, 1);
   Bind(ex, {&in_a, &in_b}, {&out}, -2, 2);
-  ex.Run(cux::OpRunMode::ON_HOST);
-  auto host = Snapshot<float>(&out);
+  std::vector<float> host;
+  if (!g_device_only) { ex.Run(cux::OpRunMode::ON_HOST); host = Snapshot<float>(&out); }
   ex.Run(cux::OpRunMode::ON_DEVICE);
-  CrossCheck("dot", host, Snapshot<float>(&out));
+  if (!g_device_only) CrossCheck("dot", host, Snapshot<float>(&out));
   Finish(ex, "dot");
 }
 
@@ -63,10 +72,10 @@ void Nrm2Test(int data_len) {
   ex.SelectOp("nrm2", "");
   cux::Array4D in(1, 1, 1, data_len), out(1, 1, 1, 1);
   Bind(ex, {&in}, {&out}, -1, 1);
-  ex.Run(cux::OpRunMode::ON_HOST);
-  auto host = Snapshot<float>(&out);
+  std::vector<float> host;
+  if (!g_device_only) { ex.Run(cux::OpRunMode::ON_HOST); host = Snapshot<float>(&out); }
   ex.Run(cux::OpRunMode::ON_DEVICE);
-  CrossCheck("nrm2", host, Snapshot<float>(&out));
+  if (!g_device_only) CrossCheck("nrm2", host, Snapshot<float>(&out));
   Finish(ex, "nrm2");
 }
 
@@ -76,28 +85,32 @@ void ReduceSumTest(int data_len) {
   ex.SelectOp("reduce_sum", "");
   cux::Array4D in(1, 1, 1, data_len), out(1, 1, 1, 1);
   Bind(ex, {&in}, {&out}, -2, 2);
-  ex.Run(cux::OpRunMode::ON_HOST);
-  auto host = Snapshot<float>(&out);
+  std::vector<float> host;
+  if (!g_device_only) { ex.Run(cux::OpRunMode::ON_HOST); host = Snapshot<float>(&out); }
   ex.Run(cux::OpRunMode::ON_DEVICE);
-  CrossCheck("reduce_sum", host, Snapshot<float>(&out));
+  if (!g_device_only) CrossCheck("reduce_sum", host, Snapshot<float>(&out));
   Finish(ex, "reduce_sum");
 }
 
-void GEMMTest(int block_size) {
+void GEMMTest(int block_size, int lo, int hi) {
   cux::Executor ex;
   ex.Initialize(0);
   ex.SelectOp("gemm", "alpha: 1.0, beta: 3.0");
   ex.AddPlugin(GemmGPUPlugin(), cux::OpRunMode::ON_DEVICE);
   cux::Array4D in_a(1, 1, block_size * 16, block_size * 15), in_b(1, 1, block_size * 15, block_size * 18);
   cux::Array4D out_c(1, 1, in_a.shape()[cux::HEIGHT], in_b.shape()[cux::WIDTH]);
-  Bind(ex, {&in_a, &in_b}, {&out_c}, -2, 5);
-  ex.Run(cux::OpRunMode::ON_HOST);
-  auto host = Snapshot<float>(&out_c);
-  out_c.Restore(cux::TypeFlag::FLOAT32, cux::ON_HOST);  // beta: the device run must start from the original C
+  Bind(ex, {&in_a, &in_b}, {&out_c}, lo, hi);
+  std::vector<float> host;
+  if (!g_device_only) {
+    ex.Run(cux::OpRunMode::ON_HOST);
+    host = Snapshot<float>(&out_c);
+    out_c.Restore(cux::TypeFlag::FLOAT32, cux::ON_HOST);  // beta: the device run must start from the original C
+  }
   ex.Run(cux::OpRunMode::ON_DEVICE);
-  // the last device kernel left its result in the fp32 host copy only if it was fp32; compare V0 explicitly
-  out_c.GetCpuData<float>(cux::PUSH);
-  CrossCheck("gemm fp32", host, Snapshot<float>(&out_c));
+  if (!g_device_only) {
+    out_c.GetCpuData<float>(cux::PUSH);
+    CrossCheck("gemm fp32", host, Snapshot<float>(&out_c));
+  }
   Finish(ex, "gemm");
 }
 
@@ -107,10 +120,10 @@ void LinearInt8Test(int M, int N, int K) {
   ex.SelectOp("linear_int8", "");
   cux::Array4D a(1, 1, M, K), bt(1, 1, N, K), c(1, 1, M, N);
   Bind(ex, {&a, &bt}, {&c}, -8, 8);
-  ex.Run(cux::OpRunMode::ON_HOST);
-  auto host = Snapshot<int32_t>(&c);
+  std::vector<int32_t> host;
+  if (!g_device_only) { ex.Run(cux::OpRunMode::ON_HOST); host = Snapshot<int32_t>(&c); }
   ex.Run(cux::OpRunMode::ON_DEVICE);
-  CrossCheck("linear_int8", host, Snapshot<int32_t>(&c));
+  if (!g_device_only) CrossCheck("linear_int8", host, Snapshot<int32_t>(&c));
   Finish(ex, "linear_int8");
 }
 
@@ -120,10 +133,10 @@ void ScanTest(int n) {
   ex.SelectOp("scan_i32", "");
   cux::Array4D in(1, 1, 1, n), out(1, 1, 1, n);
   Bind(ex, {&in}, {&out}, -2, 2);
-  ex.Run(cux::OpRunMode::ON_HOST);
-  auto host = Snapshot<int32_t>(&out);
+  std::vector<int32_t> host;
+  if (!g_device_only) { ex.Run(cux::OpRunMode::ON_HOST); host = Snapshot<int32_t>(&out); }
   ex.Run(cux::OpRunMode::ON_DEVICE);
-  CrossCheck("scan_i32", host, Snapshot<int32_t>(&out));
+  if (!g_device_only) CrossCheck("scan_i32", host, Snapshot<int32_t>(&out));
   Finish(ex, "scan_i32");
 }
 
@@ -132,10 +145,18 @@ void ScanTest(int n) {
 int main(int argc, char **argv) {
   int data_len = 4096000;  // demo.cpp:18
   int gemm_block = 32;     // demo.cpp:82
+  int lin_m = 200, lin_n = 304, lin_k = 400;  // simd/x86/linear.cpp:254 (N rounded up to a multiple of 4)
+  int scan_len = -1;
+  int gemm_lo = -2, gemm_hi = 5;  // demo.cpp:97
   for (int i = 1; i < argc; i++) {
     if (!std::strcmp(argv[i], "--len") && i + 1 < argc) data_len = std::atoi(argv[++i]);
     else if (!std::strcmp(argv[i], "--quick")) { data_len = 409600; gemm_block = 8; }
     else if (!std::strcmp(argv[i], "--device-fill")) g_device_fill = true;
+    else if (!std::strcmp(argv[i], "--device-only")) g_device_only = true;
+    else if (!std::strcmp(argv[i], "--gemm-block") && i + 1 < argc) gemm_block = std::atoi(argv[++i]);
+    else if (!std::strcmp(argv[i], "--scan-len") && i + 1 < argc) scan_len = std::atoi(argv[++i]);
+    else if (!std::strcmp(argv[i], "--gemm-range") && i + 2 < argc) { gemm_lo = std::atoi(argv[++i]); gemm_hi = std::atoi(argv[++i]); }
+    else if (!std::strcmp(argv[i], "--linear") && i + 3 < argc) { lin_m = std::atoi(argv[++i]); lin_n = std::atoi(argv[++i]); lin_k = std::atoi(argv[++i]); }
     else if (!std::strcmp(argv[i], "--pinned")) cux::Array4D::UsePinnedHostMemory(true);
   }
   cux::InitEnvironment();
@@ -145,13 +166,13 @@ int main(int argc, char **argv) {
   std::printf("\n\nNorm2Test.\n");
   Nrm2Test(data_len);
   std::printf("\n\nGEMMTest.\n");
-  GEMMTest(gemm_block);
+  GEMMTest(gemm_block, gemm_lo, gemm_hi);
   std::printf("\n\nReduceSumTest.\n");
   ReduceSumTest(data_len);
   std::printf("\n\nLinearInt8Test.\n");
-  LinearInt8Test(200, 304, 400);  // simd/x86/linear.cpp:254 (N rounded to a multiple of 4 for the int32 rows)
+  LinearInt8Test(lin_m, lin_n, lin_k);
   std::printf("\n\nScanTest.\n");
-  ScanTest(data_len);
+  ScanTest(scan_len > 0 ? scan_len : data_len);
   cux::CleanUpEnvironment();
   std::printf("\ncux_demo: %s\n", g_failures ? "FAILED" : "all checks passed");
   return g_failures ? 1 : 0;
