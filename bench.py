@@ -215,7 +215,7 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None):
             W.desc = "int8 linear %d^3 per GPU, int32 accumulate, tcgen05 kind::i8 (configs[4])" % n
             W.metric = "GEMM TOP/s (int8 linear 8192^3 per GPU, int32 accumulate)"
         W.kernel = W.step = fn
-        if name == "hgemm" and world > 1 and peers is not None:
+        if world > 1 and peers is not None:
             # B lives on rank 0 only; every other rank's GEMM kernel pulls it over NVLink while multiplying
             bsym = peers.symmetric_like(B)
             if rank == 0:
@@ -224,10 +224,21 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None):
             dist.barrier()
             is_root = rank == 0
             W.step_nccl = fn  # comparison: B already resident on every GPU (no broadcast in the step)
-            W.step = lambda: ctx.mg_hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, bsym.ptrs[0], bsym.ptrs[rank], n, 0.0,
-                                              C.data_ptr(), n, is_root, capi.FLOAT16, stream())
-            W.collective = ("fused: B (512 MiB) is pulled from rank 0 over NVLink peer memory by the GEMM kernel itself, "
-                            "panel by panel, overlapped with the mainloop (no NCCL launch); rows of C sharded")
+            if name == "hgemm":
+                W.step = lambda: ctx.mg_hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, bsym.ptrs[0], bsym.ptrs[rank], n, 0.0,
+                                                  C.data_ptr(), n, is_root, capi.FLOAT16, stream())
+                how = "by the otherwise idle warp of every CTA (TMA), column panel by column panel"
+            elif name == "sgemm":
+                W.step = lambda: ctx.mg_sgemm_f32(n, n, n, 1.0, A.data_ptr(), n, bsym.ptrs[0], bsym.ptrs[rank], n, 0.0,
+                                                  C.data_ptr(), n, is_root, stream())
+                how = "by the first 64 CTAs of the launch, 128 rows of B per readiness flag"
+            else:
+                W.step = lambda: ctx.mg_linear_s8(n, n, n, A.data_ptr(), bsym.ptrs[0], bsym.ptrs[rank], C.data_ptr(),
+                                                  is_root, stream())
+                how = "by the otherwise idle warp of every CTA (TMA), n-block panel by n-block panel"
+            W.collective = ("fused: B (%d MiB) is pulled from rank 0 over NVLink peer memory by the GEMM kernel itself, %s, "
+                            "overlapped with the mainloop (no NCCL launch); rows of C sharded"
+                            % ((B.numel() * B.element_size()) >> 20, how))
             W.keep = bsym
         W.units = 2 * n * n * n
         W.unit = "TOP/s" if name == "linear_s8" else "TFLOP/s"

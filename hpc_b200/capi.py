@@ -64,6 +64,8 @@ SIGNATURES = {
     "cuxb_mg_exscan_total_i32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
     "cuxb_mg_scan_i32": ([_vp, _vp, _ll, _vp, _vp, _i, _i, C.POINTER(_vp)], _i),
     "cuxb_mg_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i], _i),
+    "cuxb_mg_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i], _i),
+    "cuxb_mg_linear_s8_s32": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i], _i),
     "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
@@ -204,6 +206,14 @@ class Context:
                      stream=0):
         check(lib().cuxb_mg_hgemm_f16_f32acc(self._h, stream, M, N, K, alpha, A, lda, b_root, b_local, ldb, beta, Cp,
                                              ldc, c_dtype, int(is_root)), "cuxb_mg_hgemm_f16_f32acc")
+
+    def mg_sgemm_f32(self, M, N, K, alpha, A, lda, b_root, b_local, ldb, beta, Cp, ldc, is_root, stream=0):
+        check(lib().cuxb_mg_sgemm_f32(self._h, stream, M, N, K, alpha, A, lda, b_root, b_local, ldb, beta, Cp, ldc,
+                                      int(is_root)), "cuxb_mg_sgemm_f32")
+
+    def mg_linear_s8(self, M, N, K, A, bt_root, bt_local, Cp, is_root, stream=0):
+        check(lib().cuxb_mg_linear_s8_s32(self._h, stream, M, N, K, A, bt_root, bt_local, Cp, int(is_root)),
+              "cuxb_mg_linear_s8_s32")
 
     def convert(self, n, src, src_dtype, dst, dst_dtype, stream=0):
         check(lib().cuxb_convert(self._h, stream, n, src, src_dtype, dst, dst_dtype), "cuxb_convert")

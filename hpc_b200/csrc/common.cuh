@@ -75,10 +75,14 @@ struct cuxb_ctx {
   int *mg_seed;                // device int32: the sharded scan's exclusive offset
   unsigned int *bcast_ready;   // fused B broadcast: per-panel arrival counters (grow by grid size per call)
   unsigned int bcast_calls;
-  int bcast_grid;
+  int bcast_grid, bcast_panels;
   // sgemm split-K: parked accumulators + per-tile tickets
   void *sg_scratch;
   size_t sg_scratch_bytes;
+  // sgemm fused B broadcast: [0,4096) per-panel arrival counters, [4096] role ticket
+  unsigned int *sg_pull;
+  unsigned int sg_pull_calls, sg_pull_ticket_base;
+  int sg_pull_panels;
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];

@@ -96,6 +96,7 @@ CUXB_API int cuxb_ctx_destroy(cuxb_ctx *c) {
   if (c->scan_state) cudaFree(c->scan_state);
   if (c->bcast_ready) cudaFree(c->bcast_ready);
   if (c->sg_scratch) cudaFree(c->sg_scratch);
+  if (c->sg_pull) cudaFree(c->sg_pull);
   for (int i = 0; i < 4; i++)
     if (c->stage[i]) cudaFree(c->stage[i]);
   if (c->stage_stream) cudaStreamDestroy(c->stage_stream);

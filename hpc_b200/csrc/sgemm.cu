@@ -47,14 +47,81 @@ struct SgemmArgs {
   int splits, k_per_split;
   float4 *scratch;        // [tile][split][16][256] float4
   unsigned int *tickets;  // [tile], zero at rest
+  // fused B broadcast (PULL instantiation, multi-GPU non-root ranks): the first kSgPullCtas CTAs to
+  // start copy B from the root GPU (Bsrc, peer memory) into B, k-panel by k-panel; the others multiply
+  // and wait for pull_ready[panel] to reach ready_target before loading rows of that panel.
+  const float *Bsrc;
+  unsigned int *pull_ready;   // [panel], grows by kSgPullCtas per call
+  unsigned int *pull_ticket;  // role ticket, grows by the grid size per call
+  unsigned int ticket_base, ready_target;
+  int panels;
 };
 
-template <bool FAST, bool SPLITK>
+constexpr int kSgPullCtas = 64;     // 64 x 256 threads x 8 x 16 B = 2 MiB in flight over NVLink
+constexpr int kSgPullPanelK = 128;  // rows of B per readiness flag
+
+__device__ __forceinline__ unsigned int sg_ld_acquire(const unsigned int *p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long sg_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// One copy CTA's share of the broadcast: float4 e of a panel (row-major over rows x N/4) belongs to
+// CTA (e / 256) mod kSgPullCtas; eight loads in flight per thread.
+__device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
+  const int tid = threadIdx.x;
+  const int n4 = p.N >> 2;
+  constexpr int kStride = kSgPullCtas * SG_THREADS;
+  for (int pnl = 0; pnl < p.panels; pnl++) {
+    const int r0 = pnl * kSgPullPanelK;
+    const int rows = min(kSgPullPanelK, p.K - r0);
+    const int total = rows * n4;  // < 2^31 (checked on the host)
+    for (int e0 = c * SG_THREADS + tid; e0 < total; e0 += 8 * kStride) {
+      float4 v[8];
+      size_t off[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        const int e = e0 + u * kStride;
+        const int row = e / n4, col4 = e - row * n4;
+        off[u] = (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4;
+        if (e < total)
+          asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(p.Bsrc + off[u]) : "memory");
+      }
+#pragma unroll
+      for (int u = 0; u < 8; u++)
+        if (e0 + u * kStride < total) *reinterpret_cast<float4 *>(const_cast<float *>(p.B) + off[u]) = v[u];
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.pull_ready + pnl) : "memory");
+  }
+}
+
+template <bool FAST, bool SPLITK, bool PULL = false>
 __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p) {
   __shared__ __align__(16) float As[2][SG_BK][SG_LDA];
   __shared__ __align__(16) float Bs[2][SG_BK][SG_BN];
 
   const int tid = threadIdx.x;
+  int block_id = blockIdx.x;
+  if constexpr (PULL) {
+    // roles by order of arrival, so the copy CTAs are running before anything waits for them
+    __shared__ unsigned int s_slot;
+    if (tid == 0) s_slot = atomicAdd(p.pull_ticket, 1u) - p.ticket_base;
+    __syncthreads();
+    const unsigned int slot = s_slot;
+    if (slot < (unsigned int)kSgPullCtas) {
+      sgemm_pull_b(p, (int)slot);
+      return;
+    }
+    block_id = (int)slot - kSgPullCtas;
+  }
   const int lane = tid & 31, warp = tid >> 5;
   const int warp_m = warp >> 2, warp_n = warp & 3;   // 2 x 4 warps
   // 8 x 4 lanes.  An LDS.128 costs max(2, distinct 16-byte chunks per 4-lane group) wavefronts
@@ -67,8 +134,8 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   const int tn0 = warp_n * 32 + lane_n * 4;
 
   // grouped rasterisation
-  const int pid = SPLITK ? blockIdx.x / p.splits : blockIdx.x;
-  const int split = SPLITK ? blockIdx.x - pid * p.splits : 0;
+  const int pid = SPLITK ? block_id / p.splits : block_id;
+  const int split = SPLITK ? block_id - pid * p.splits : 0;
   const int k_begin = SPLITK ? split * p.k_per_split : 0;
   const int k_end = SPLITK ? min(p.K, k_begin + p.k_per_split) : p.K;
   const int per_group = SG_GROUP_M * p.tiles_n;
@@ -138,7 +205,19 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc2[i][j] = make_float2(0.f, 0.f);
 
+  // PULL: rows [q*128, q*128+128) of B may be read once every copy CTA has delivered its share of panel q
+  int panels_known = 0;
+  auto need_panel = [&](int k0) {
+    const int q = k0 / kSgPullPanelK;
+    if (q < panels_known) return;
+    const unsigned long long t0 = sg_timer_ns();
+    while ((int)(sg_ld_acquire(p.pull_ready + q) - p.ready_target) < 0)
+      if (sg_timer_ns() - t0 > 20000000000ull) __trap();
+    panels_known = q + 1;
+  };
+
   const int KT = (max(k_end - k_begin, 0) + SG_BK - 1) / SG_BK;
+  if constexpr (PULL) need_panel(k_begin);
   gload(k_begin, 0);
   sstore(0);
   __syncthreads();
@@ -159,6 +238,9 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   for (int kt = 0; kt < KT; kt++) {
     const int buf = kt & 1;
     const bool more = kt + 1 < KT;
+    if constexpr (PULL) {
+      if (more) need_panel(k_begin + (kt + 1) * SG_BK);
+    }
     if (more) gload(k_begin + (kt + 1) * SG_BK, buf ^ 1);
     lfrag(buf, 0, 0);
 #pragma unroll
@@ -281,6 +363,7 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
   // split-K when the tiles alone would leave most of the GPU idle (room: 2 CTAs per SM) -- the
   // 64 x 4096 x 64 case of cuda/gemm_fp32.cu:162-258,714-718 and cux's demo shape
   p.splits = 1, p.k_per_split = K > 0 ? K : 1, p.scratch = nullptr, p.tickets = nullptr;
+  p.Bsrc = nullptr, p.pull_ready = nullptr, p.pull_ticket = nullptr, p.ticket_base = 0, p.ready_target = 0, p.panels = 0;
   const int room = 2 * ctx->sm_count;  // CTAs resident at once
   int splits = 1;
   if (tiles <= 1024 && K >= 256) {
@@ -327,6 +410,62 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
     if (fast) sgemm_kernel<true, false><<<grid, SG_THREADS, 0, st>>>(p);
     else sgemm_kernel<false, false><<<grid, SG_THREADS, 0, st>>>(p);
   }
+  CUXB_LAUNCHED();
+  return 0;
+}
+
+// Row-sharded SGEMM with the broadcast of B fused into the kernel (mpi/alg_matrix_multiply.cpp:52-74:
+// B to every worker, row blocks of A and C).  The root multiplies with b_root in place.  On any other
+// rank the first 64 CTAs of the launch copy B from the root's memory (b_root as mapped into this
+// process) into b_local, 128 rows of B at a time, and every other CTA multiplies, waiting only for the
+// k-panel it is about to load.  Needs the vectorised path: M, N multiples of 128, K of 16, lda/ldb/ldc
+// multiples of 4, 16-byte aligned pointers.
+CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const float *A,
+                               int lda, const float *b_root, float *b_local, int ldb, float beta, float *C,
+                               int ldc, int is_root) {
+  if (is_root) return cuxb_sgemm_f32(ctx, stream, M, N, K, alpha, A, lda, b_root, ldb, beta, C, ldc);
+  int rc = ensure_device(ctx);
+  if (rc) return rc;
+  CUXB_REQUIRE(M >= 0 && N >= 0 && K >= 0, CUXB_ERR_INVALID, "cuxb_mg_sgemm_f32: negative dimension");
+  if (M == 0 || N == 0) return 0;
+  CUXB_REQUIRE(A && b_root && b_local && C, CUXB_ERR_INVALID, "cuxb_mg_sgemm_f32: null pointer");
+  CUXB_REQUIRE(lda >= K && ldb >= N && ldc >= N, CUXB_ERR_INVALID,
+               "cuxb_mg_sgemm_f32: leading dimension smaller than the row length");
+  const bool fast = (M % SG_BM == 0) && (N % SG_BN == 0) && (K % SG_BK == 0) && K > 0 && (lda % 4 == 0) &&
+                    (ldb % 4 == 0) && (ldc % 4 == 0) &&
+                    ((((uintptr_t)A | (uintptr_t)b_root | (uintptr_t)b_local | (uintptr_t)C) & 15) == 0);
+  CUXB_REQUIRE(fast, CUXB_ERR_UNSUPPORTED,
+               "cuxb_mg_sgemm_f32: needs M,N %% 128 == 0, K %% 16 == 0, lda/ldb/ldc %% 4 == 0 and 16-byte aligned pointers");
+  SgemmArgs p;
+  p.M = M, p.N = N, p.K = K, p.alpha = alpha, p.beta = beta;
+  p.A = A, p.lda = lda, p.B = b_local, p.ldb = ldb, p.C = C, p.ldc = ldc;
+  p.tiles_m = M / SG_BM, p.tiles_n = N / SG_BN;
+  p.splits = 1, p.k_per_split = K, p.scratch = nullptr, p.tickets = nullptr;
+  p.panels = (K + kSgPullPanelK - 1) / kSgPullPanelK;
+  CUXB_REQUIRE(p.panels <= 4096 && (long long)kSgPullPanelK * (N / 4) < (1ll << 31), CUXB_ERR_TOO_LARGE,
+               "cuxb_mg_sgemm_f32: K or N too large for the fused broadcast");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (ctx->sg_pull == nullptr) {
+    CUXB_CUDA(cudaMalloc((void **)&ctx->sg_pull, (4096 + 32) * sizeof(unsigned int)));
+    CUXB_CUDA(cudaMemset(ctx->sg_pull, 0, (4096 + 32) * sizeof(unsigned int)));
+    ctx->sg_pull_calls = 0, ctx->sg_pull_ticket_base = 0, ctx->sg_pull_panels = 0;
+  }
+  // the flags only grow, by 64 per call for each of the call's panels: a different panel count would
+  // leave them uneven, so start over from zero when it changes (ordered on the stream)
+  if (ctx->sg_pull_panels != p.panels) {
+    CUXB_CUDA(cudaMemsetAsync(ctx->sg_pull, 0, 4096 * sizeof(unsigned int), st));
+    ctx->sg_pull_calls = 0;
+    ctx->sg_pull_panels = p.panels;
+  }
+  const unsigned int grid = (unsigned int)(p.tiles_m * p.tiles_n + kSgPullCtas);
+  p.Bsrc = b_root;
+  p.pull_ready = ctx->sg_pull;
+  p.pull_ticket = ctx->sg_pull + 4096;
+  p.ticket_base = ctx->sg_pull_ticket_base;
+  ctx->sg_pull_ticket_base += grid;                      // unsigned wrap-around is fine
+  ctx->sg_pull_calls++;
+  p.ready_target = ctx->sg_pull_calls * (unsigned int)kSgPullCtas;
+  sgemm_kernel<true, false, true><<<grid, SG_THREADS, 0, st>>>(p);
   CUXB_LAUNCHED();
   return 0;
 }

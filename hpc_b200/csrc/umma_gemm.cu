@@ -427,30 +427,43 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else if (warp == 3) {
     // ===================== broadcast warp (multi-GPU, non-root ranks only) =====================
     // Pulls B from the root GPU's memory over NVLink into the local copy, panel by panel in the
-    // order the tiles consume them: TMA load (peer global -> shared, 256 columns x 24 rows), TMA store
-    // (shared -> local global), two boxes in flight.  Box c of a panel belongs to CTA (c mod grid).
-    // When this CTA's share of a panel has landed it bumps the panel's counter (release).
+    // order the tiles consume them (panel = the 256 output columns of one n-block): TMA load (peer
+    // global -> shared), TMA store (shared -> local global), two boxes in flight.  B[K,N] (B_MN): a
+    // panel is 256 columns x K rows, boxes of 256 columns x 24 rows.  Bt[N,K] (K-major): a panel is
+    // 256 rows x K columns, boxes of 256 k x kPullRows rows.  Box c of a panel belongs to CTA
+    // (c mod grid).  When this CTA's share of a panel has landed it bumps the panel's counter (release).
     if (p.b_ready != nullptr && elect_one()) {
-      constexpr int kBoxRows = 24;
-      const int boxes_per_panel = (p.K + kBoxRows - 1) / kBoxRows;
+      constexpr int kPullRows = B_MN ? 24 : (KIND == KIND_S8 ? 32 : 16);
+      constexpr uint32_t kPullBytes = 256u * kPullRows * (KIND == KIND_S8 ? 1 : 2);
+      static_assert(kPullBytes <= (uint32_t)Cfg::kCopyBufBytes, "broadcast staging buffer too small");
+      constexpr int kRowBoxes = UG_BLOCK_N / kPullRows;          // K-major only: row chunks per panel
+      const int boxes_per_panel = B_MN ? (p.K + kPullRows - 1) / kPullRows : ((p.K + 255) / 256) * kRowBoxes;
       const int G = gridDim.x, me = blockIdx.x;
       const int mine_per_panel = (boxes_per_panel - me + G - 1) / G;  // boxes c = me, me+G, ... < boxes_per_panel
       const long long total = (long long)mine_per_panel * p.tiles_n;
+      auto coords = [&](long long i, int &panel, int &x, int &y) {
+        panel = (int)(i / mine_per_panel);
+        const int c = me + (int)(i % mine_per_panel) * G;
+        if (B_MN) x = panel * UG_BLOCK_N, y = c * kPullRows;
+        else x = (c / kRowBoxes) * 256, y = panel * UG_BLOCK_N + (c % kRowBoxes) * kPullRows;
+      };
       auto issue = [&](long long i) {
-        const int panel = (int)(i / mine_per_panel), c = me + (int)(i % mine_per_panel) * G;
+        int panel, x, y;
+        coords(i, panel, x, y);
         const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
-        mbar_expect_tx(bar, Cfg::kCopyBufBytes);
+        mbar_expect_tx(bar, kPullBytes);
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                     ::"r"(buf), "l"(&map_bsrc), "r"(bar), "r"(panel * UG_BLOCK_N), "r"(c * kBoxRows) : "memory");
+                     ::"r"(buf), "l"(&map_bsrc), "r"(bar), "r"(x), "r"(y) : "memory");
       };
       if (total > 0) issue(0);
       if (total > 1) issue(1);
       for (long long i = 0; i < total; i++) {
-        const int panel = (int)(i / mine_per_panel), c = me + (int)(i % mine_per_panel) * G;
+        int panel, x, y;
+        coords(i, panel, x, y);
         const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
         mbar_wait(bar, (uint32_t)((i >> 1) & 1));
         asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
-                     ::"l"(&map_bdst), "r"(buf), "r"(panel * UG_BLOCK_N), "r"(c * kBoxRows) : "memory");
+                     ::"l"(&map_bdst), "r"(buf), "r"(x), "r"(y) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         const bool last_of_panel = ((i + 1) % mine_per_panel) == 0;
         if (last_of_panel) {
@@ -606,26 +619,29 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   if (clusters > total) clusters = total;
 
   CUtensorMap msrc = mb, mdst = mb;  // unused unless B is pulled from another GPU
-  if constexpr (!(B_MN && ebytes == 2)) {
-    CUXB_REQUIRE(b_pull_from == nullptr, CUXB_ERR_UNSUPPORTED, "fused B broadcast: 16-bit B[K,N] layout only");
-  } else if (b_pull_from != nullptr) {
+  if (b_pull_from != nullptr) {
     CUXB_REQUIRE(p.tiles_n <= 4096, CUXB_ERR_TOO_LARGE, "fused B broadcast: N too large");
-    rc = make_map(ctx, &msrc, b_pull_from, ebytes, dt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, UG_BLOCK_N, 24, false);
+    // un-swizzled copy boxes (see the broadcast warp): 256 elements wide, 24 / 32 / 16 rows
+    const uint64_t rows = B_MN ? (uint64_t)K : (uint64_t)N, cols = B_MN ? (uint64_t)N : (uint64_t)K;
+    const uint32_t box_rows = B_MN ? 24 : (KIND == KIND_S8 ? 32 : 16);
+    rc = make_map(ctx, &msrc, b_pull_from, ebytes, dt, rows, cols, (uint64_t)ldb, 256, box_rows, false);
     if (rc) return rc;
-    rc = make_map(ctx, &mdst, B, ebytes, dt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, UG_BLOCK_N, 24, false);
+    rc = make_map(ctx, &mdst, B, ebytes, dt, rows, cols, (uint64_t)ldb, 256, box_rows, false);
     if (rc) return rc;
     if (ctx->bcast_ready == nullptr) {
       CUXB_CUDA(cudaMalloc((void **)&ctx->bcast_ready, 4096 * sizeof(unsigned int)));
       CUXB_CUDA(cudaMemset(ctx->bcast_ready, 0, 4096 * sizeof(unsigned int)));
       ctx->bcast_calls = 0;
       ctx->bcast_grid = 0;
+      ctx->bcast_panels = 0;
     }
-    // counters only grow: every copy warp adds 1 per panel per call.  A different grid size would
-    // break the arithmetic, so start over from zero when it changes.
-    if (ctx->bcast_grid != clusters * CG) {
+    // counters only grow: every copy warp adds 1 to each of the call's panels.  A different grid size
+    // or panel count would break the arithmetic, so start over from zero when either changes.
+    if (ctx->bcast_grid != clusters * CG || ctx->bcast_panels != p.tiles_n) {
       CUXB_CUDA(cudaMemsetAsync(ctx->bcast_ready, 0, 4096 * sizeof(unsigned int), st));
       ctx->bcast_calls = 0;
       ctx->bcast_grid = clusters * CG;
+      ctx->bcast_panels = p.tiles_n;
     }
     ctx->bcast_calls++;
     p.b_ready = ctx->bcast_ready;
@@ -775,4 +791,19 @@ CUXB_API int cuxb_mg_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N,
   if (c_dtype == CUXB_FLOAT16)
     return launch_umma<KIND_F16, true, CUXB_FLOAT16, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, pull);
   return launch_umma<KIND_F16, true, CUXB_FLOAT32, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, pull);
+}
+
+// Row-sharded int8 linear with the broadcast of Bt fused into the kernel (the same decomposition, for
+// simd/x86/linear.cpp:199-211's C = A * Bt^T): Bt[N,K] lives on the root; every other rank's kernel
+// pulls it over NVLink, n-block panel by n-block panel, while multiplying the panels that arrived.
+CUXB_API int cuxb_mg_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, int K, const int8_t *A,
+                                   const int8_t *bt_root, int8_t *bt_local, int32_t *C, int is_root) {
+  const void *Bt = is_root ? (const void *)bt_root : (const void *)bt_local;
+  int rc = check_common("cuxb_mg_linear_s8_s32", ctx, M, N, K, A, Bt, C, 1, K, K, N, 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  CUXB_REQUIRE(bt_root != nullptr && ((uintptr_t)bt_root & 15) == 0, CUXB_ERR_INVALID,
+               "cuxb_mg_linear_s8_s32: bt_root is null or not 16-byte aligned");
+  const void *pull = is_root ? nullptr : (const void *)bt_root;
+  return launch_umma<KIND_S8, false, CUXB_INT32, 2>(ctx, (cudaStream_t)stream, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N,
+                                                    pull);
 }

@@ -125,3 +125,50 @@ def test_fused_b_broadcast_gemm_two_gpus():
         for r in range(world):
             want = oracle.hgemm_f16(A[r], B16, threads=8)
             assert np.array_equal(dC[r].cpu().numpy().view(np.uint16), want), "rank %d rep %d" % (r, rep)
+
+
+def test_fused_b_broadcast_sgemm_and_int8_two_gpus():
+    """Row-sharded fp32 SGEMM and int8 linear: rank 1's launch copies B from rank 0 over NVLink (copy CTAs /
+    the idle warp) while its other CTAs multiply the panels that have arrived."""
+    world = 2
+    ctxs, _, _ = _setup(world)
+    # ---- fp32
+    M, N, K = 1024, 1152, 528
+    A = [dg.int_fill((M, K), -2, 5, tag=70 + r) for r in range(world)]
+    B = dg.int_fill((K, N), -2, 5, tag=75)
+    dA = [torch.from_numpy(A[r]).to("cuda:%d" % r) for r in range(world)]
+    dB_root = torch.from_numpy(B).to("cuda:0")
+    dB_local = torch.zeros((K, N), device="cuda:1")
+    dC = [torch.zeros((M, N), device="cuda:%d" % r) for r in range(world)]
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    for rep in range(3):
+        dB_local.zero_()
+        torch.cuda.synchronize(1)
+        ctxs[0].mg_sgemm_f32(M, N, K, 1.0, dA[0].data_ptr(), K, dB_root.data_ptr(), 0, N, 0.0, dC[0].data_ptr(), N, True)
+        ctxs[1].mg_sgemm_f32(M, N, K, 1.0, dA[1].data_ptr(), K, dB_root.data_ptr(), dB_local.data_ptr(), N, 0.0,
+                             dC[1].data_ptr(), N, False)
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        assert np.array_equal(dB_local.cpu().numpy(), B)
+        for r in range(world):
+            want = oracle.gemm_f32(A[r], B, np.zeros((M, N), np.float32), 1.0, 0.0, order="ikj", threads=8)
+            assert np.array_equal(dC[r].cpu().numpy().view(np.uint32), want.view(np.uint32)), "rank %d rep %d" % (r, rep)
+    # ---- int8
+    M, N, K = 512, 1100, 2064
+    A8 = [dg.int_fill((M, K), -128, 127, tag=80 + r).astype(np.int8) for r in range(world)]
+    Bt = dg.int_fill((N, K), -128, 127, tag=85).astype(np.int8)
+    dA8 = [torch.from_numpy(A8[r]).to("cuda:%d" % r) for r in range(world)]
+    dBt_root = torch.from_numpy(Bt).to("cuda:0")
+    dBt_local = torch.zeros((N, K), dtype=torch.int8, device="cuda:1")
+    dC8 = [torch.zeros((M, N), dtype=torch.int32, device="cuda:%d" % r) for r in range(world)]
+    for rep in range(3):
+        dBt_local.zero_()
+        torch.cuda.synchronize(1)
+        ctxs[0].mg_linear_s8(M, N, K, dA8[0].data_ptr(), dBt_root.data_ptr(), 0, dC8[0].data_ptr(), True)
+        ctxs[1].mg_linear_s8(M, N, K, dA8[1].data_ptr(), dBt_root.data_ptr(), dBt_local.data_ptr(), dC8[1].data_ptr(), False)
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        assert np.array_equal(dBt_local.cpu().numpy(), Bt)
+        for r in range(world):
+            assert np.array_equal(dC8[r].cpu().numpy(), oracle.linear_s8(A8[r], Bt, threads=8)), "rank %d rep %d" % (r, rep)

@@ -1,0 +1,144 @@
+"""GPU (one device is enough): the GEMM kernels whose broadcast of B is fused into the launch
+(cuxb_mg_sgemm_f32, cuxb_mg_linear_s8_s32, cuxb_mg_hgemm_f16_f32acc).  On a non-root rank part of the
+launch copies B from the root's memory while the rest multiplies the panels that have arrived.  The copy
+does not care where the source lives, so here the "root's B" is simply another buffer on the same GPU:
+the panel flags, the role tickets and the arithmetic are exactly those of the multi-GPU run
+(tests/test_gpu_multi.py repeats it across two devices over NVLink).
+
+Bar: the local copy of B equals the root's byte for byte, C is BIT-EXACT against the oracle / the
+single-GPU kernel, on repeated calls (the flags only grow) and on shapes with more CTAs than the GPU holds."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from hpc_b200 import capi
+from hpc_b200 import datagen as dg
+from gpu_util import bits32, ctx, dev, host, sync
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("shape,pad", [((256, 384, 400), 0), ((128, 128, 16), 0), ((384, 256, 272), 8)])
+def test_sgemm_pull_small_vs_oracle(shape, pad):
+    M, N, K = shape
+    ldb = N + pad
+    A, B, C = dg.int_fill((M, K), -2, 5, tag=11), dg.int_fill((K, N), -2, 5, tag=12), dg.int_fill((M, N), -2, 5, tag=13)
+    want = oracle.gemm_f32(A, B, C, 1.0, 3.0, order="ikj", threads=8)
+    Bp = np.full((K, ldb), 77.0, np.float32)
+    Bp[:, :N] = B
+    dA, dBroot = dev(A), dev(Bp)
+    for rep in range(3):
+        dBloc = torch.full((K, ldb), -5.0, device="cuda")
+        dC = dev(C)
+        sync()
+        ctx().mg_sgemm_f32(M, N, K, 1.0, dA.data_ptr(), K, dBroot.data_ptr(), dBloc.data_ptr(), ldb, 3.0,
+                           dC.data_ptr(), N, False)
+        sync()
+        got_b = host(dBloc)
+        assert np.array_equal(got_b[:, :N], B), "rep %d" % rep
+        if pad:
+            assert np.all(got_b[:, N:] == -5.0)          # the padding columns are not touched
+        assert np.array_equal(bits32(host(dC)), bits32(want)), "rep %d" % rep
+
+
+def test_sgemm_pull_many_waves_vs_single_gpu_kernel():
+    M, N, K = 2560, 2048, 1040   # 320 tiles + 64 copy CTAs > 296 resident; K = 8 panels + a 16-row tail
+    g = torch.Generator(device="cuda")
+    g.manual_seed(5)
+    A = torch.randint(-2, 6, (M, K), device="cuda", generator=g).float()
+    B = torch.randint(-2, 6, (K, N), device="cuda", generator=g).float()
+    C0 = torch.randint(-2, 6, (M, N), device="cuda", generator=g).float()
+    want = C0.clone()
+    ctx().sgemm_f32(M, N, K, 2.0, A.data_ptr(), K, B.data_ptr(), N, -1.0, want.data_ptr(), N)
+    for rep in range(2):
+        Bl = torch.zeros_like(B)
+        got = C0.clone()
+        sync()
+        ctx().mg_sgemm_f32(M, N, K, 2.0, A.data_ptr(), K, B.data_ptr(), Bl.data_ptr(), N, -1.0, got.data_ptr(), N, False)
+        sync()
+        assert torch.equal(Bl, B)
+        assert torch.equal(got, want)
+    # the root's call is the plain kernel
+    got = C0.clone()
+    ctx().mg_sgemm_f32(M, N, K, 2.0, A.data_ptr(), K, B.data_ptr(), 0, N, -1.0, got.data_ptr(), N, True)
+    sync()
+    assert torch.equal(got, want)
+
+
+def test_sgemm_pull_rejects_ragged_shapes():
+    t = torch.zeros(256 * 256, device="cuda")
+    with pytest.raises(capi.CuxbError, match="128"):
+        ctx().mg_sgemm_f32(100, 128, 16, 1.0, t.data_ptr(), 16, t.data_ptr(), t.data_ptr(), 128, 0.0, t.data_ptr(), 128,
+                           False)
+    with pytest.raises(capi.CuxbError):
+        ctx().mg_sgemm_f32(128, 128, 16, 1.0, t.data_ptr(), 16, 0, t.data_ptr(), 128, 0.0, t.data_ptr(), 128, False)
+
+
+@pytest.mark.parametrize("shape", [(512, 600, 1008), (256, 256, 256), (128, 4, 16), (300, 2304, 4096)])
+def test_linear_s8_pull_bit_exact(shape):
+    M, N, K = shape
+    A = dg.int_fill((M, K), -128, 127, tag=21).astype(np.int8)
+    Bt = dg.int_fill((N, K), -128, 127, tag=22).astype(np.int8)
+    want = oracle.linear_s8(A, Bt, threads=8)
+    dA, dBroot = dev(A), dev(Bt)
+    for rep in range(3):
+        dBloc = torch.full((N, K), 3, dtype=torch.int8, device="cuda")
+        dC = torch.full((M, N), -1, dtype=torch.int32, device="cuda")
+        sync()
+        ctx().mg_linear_s8(M, N, K, dA.data_ptr(), dBroot.data_ptr(), dBloc.data_ptr(), dC.data_ptr(), False)
+        sync()
+        assert np.array_equal(host(dBloc), Bt), "rep %d" % rep
+        assert np.array_equal(host(dC), want), "rep %d" % rep
+    dC = torch.full((M, N), -1, dtype=torch.int32, device="cuda")
+    ctx().mg_linear_s8(M, N, K, dA.data_ptr(), dBroot.data_ptr(), 0, dC.data_ptr(), True)   # root: in place
+    sync()
+    assert np.array_equal(host(dC), want)
+
+
+def test_hgemm_pull_same_device():
+    M, N, K = 512, 1280, 1000
+    A = oracle.f32_to_f16(dg.int_fill((M, K), -10, 9, tag=31))
+    B = oracle.f32_to_f16(dg.int_fill((K, N), -10, 9, tag=32))
+    want = oracle.hgemm_f16(A, B, threads=8)
+    dA, dBroot = dev(A), dev(B)
+    for rep in range(2):
+        dBloc = torch.zeros((K, N), dtype=torch.int16, device="cuda")
+        dC = torch.zeros((M, N), dtype=torch.int16, device="cuda")
+        sync()
+        ctx().mg_hgemm_f16(M, N, K, 1.0, dA.data_ptr(), K, dBroot.data_ptr(), dBloc.data_ptr(), N, 0.0, dC.data_ptr(), N,
+                           False)
+        sync()
+        assert np.array_equal(host(dBloc, np.uint16), B)
+        assert np.array_equal(host(dC, np.uint16), want)
+
+
+def test_pull_flags_survive_a_change_of_panel_count():
+    """Same grid (148 CTAs), different number of B panels from one call to the next: the readiness flags
+    are per panel and only grow, so the library has to notice and start them over."""
+    M, K = 4096, 256
+    g = torch.Generator(device="cuda")
+    g.manual_seed(9)
+    A = torch.randint(-10, 10, (M, K), device="cuda", generator=g).half()
+    for N in (1280, 2304, 1280, 768):
+        B = torch.randint(-10, 10, (K, N), device="cuda", generator=g).half()
+        want = torch.zeros((M, N), dtype=torch.float16, device="cuda")
+        ctx().hgemm_f16(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), N, 0.0, want.data_ptr(), N, capi.FLOAT16)
+        Bl = torch.zeros_like(B)
+        got = torch.zeros_like(want)
+        sync()
+        ctx().mg_hgemm_f16(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), Bl.data_ptr(), N, 0.0, got.data_ptr(), N, False)
+        sync()
+        assert torch.equal(Bl, B) and torch.equal(got, want), N
+    Af = A.float()
+    for Kf in (256, 128, 256):
+        B = torch.randint(-2, 6, (Kf, 1280), device="cuda", generator=g).float()
+        want = torch.zeros((M, 1280), device="cuda")
+        ctx().sgemm_f32(M, 1280, Kf, 1.0, Af.data_ptr(), K, B.data_ptr(), 1280, 0.0, want.data_ptr(), 1280)
+        Bl = torch.zeros_like(B)
+        got = torch.zeros_like(want)
+        sync()
+        ctx().mg_sgemm_f32(M, 1280, Kf, 1.0, Af.data_ptr(), K, B.data_ptr(), Bl.data_ptr(), 1280, 0.0, got.data_ptr(),
+                           1280, False)
+        sync()
+        assert torch.equal(Bl, B) and torch.equal(got, want), Kf
