@@ -231,7 +231,7 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None):
             elif name == "sgemm":
                 W.step = lambda: ctx.mg_sgemm_f32(n, n, n, 1.0, A.data_ptr(), n, bsym.ptrs[0], bsym.ptrs[rank], n, 0.0,
                                                   C.data_ptr(), n, is_root, stream())
-                how = "by the first 64 CTAs of the launch, 128 rows of B per readiness flag"
+                how = "by the first 48 CTAs of the launch (the slots its last wave of tiles leaves idle), 128 rows of B per readiness flag"
             else:
                 W.step = lambda: ctx.mg_linear_s8(n, n, n, A.data_ptr(), bsym.ptrs[0], bsym.ptrs[rank], C.data_ptr(),
                                                   is_root, stream())

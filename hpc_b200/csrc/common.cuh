@@ -82,7 +82,7 @@ struct cuxb_ctx {
   // sgemm fused B broadcast: [0,4096) per-panel arrival counters, [4096] role ticket
   unsigned int *sg_pull;
   unsigned int sg_pull_calls, sg_pull_ticket_base;
-  int sg_pull_panels;
+  int sg_pull_panels, sg_pull_ncopy;
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];

@@ -47,18 +47,18 @@ struct SgemmArgs {
   int splits, k_per_split;
   float4 *scratch;        // [tile][split][16][256] float4
   unsigned int *tickets;  // [tile], zero at rest
-  // fused B broadcast (PULL instantiation, multi-GPU non-root ranks): the first kSgPullCtas CTAs to
-  // start copy B from the root GPU (Bsrc, peer memory) into B, k-panel by k-panel; the others multiply
-  // and wait for pull_ready[panel] to reach ready_target before loading rows of that panel.
+  // fused B broadcast (PULL instantiation, multi-GPU non-root ranks): the first n_copy CTAs to start
+  // copy B from the root GPU (Bsrc, peer memory) into B, k-panel by k-panel, and exit; the others
+  // multiply and wait for pull_ready[panel] to reach ready_target before loading rows of that panel.
   const float *Bsrc;
-  unsigned int *pull_ready;   // [panel], grows by kSgPullCtas per call
-  unsigned int *pull_ticket;  // role ticket, grows by the grid size per call
+  unsigned int *pull_ready;   // [panel], grows by n_copy per call
+  unsigned int *pull_ticket;  // arrival ticket, grows by the grid size per call
   unsigned int ticket_base, ready_target;
-  int panels;
+  int panels, n_copy;
 };
 
-constexpr int kSgPullCtas = 64;     // 64 x 256 threads x 8 x 16 B = 2 MiB in flight over NVLink
-constexpr int kSgPullPanelK = 128;  // rows of B per readiness flag
+constexpr int kSgPullInFlight = 16;  // 16-byte loads in flight per thread: 64 KiB per copy CTA over NVLink
+constexpr int kSgPullPanelK = 128;   // rows of B per readiness flag
 
 __device__ __forceinline__ unsigned int sg_ld_acquire(const unsigned int *p) {
   unsigned int v;
@@ -72,30 +72,37 @@ __device__ __forceinline__ unsigned long long sg_timer_ns() {
 }
 
 // One copy CTA's share of the broadcast: float4 e of a panel (row-major over rows x N/4) belongs to
-// CTA (e / 256) mod kSgPullCtas; eight loads in flight per thread.
+// CTA (e / 256) mod n_copy; sixteen loads in flight per thread.
 __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
   const int tid = threadIdx.x;
   const int n4 = p.N >> 2;
-  constexpr int kStride = kSgPullCtas * SG_THREADS;
+  const int stride = p.n_copy * SG_THREADS;
+  const float *src = p.Bsrc;
+  float *dst = const_cast<float *>(p.B);
   for (int pnl = 0; pnl < p.panels; pnl++) {
     const int r0 = pnl * kSgPullPanelK;
     const int rows = min(kSgPullPanelK, p.K - r0);
-    const int total = rows * n4;  // < 2^31 (checked on the host)
-    for (int e0 = c * SG_THREADS + tid; e0 < total; e0 += 8 * kStride) {
-      float4 v[8];
-      size_t off[8];
+    const long long total = (long long)rows * n4;  // < 2^31 (checked on the host)
+    for (long long e0 = c * SG_THREADS + tid; e0 < total; e0 += (long long)kSgPullInFlight * stride) {
+      float4 v[kSgPullInFlight];
 #pragma unroll
-      for (int u = 0; u < 8; u++) {
-        const int e = e0 + u * kStride;
-        const int row = e / n4, col4 = e - row * n4;
-        off[u] = (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4;
-        if (e < total)
+      for (int u = 0; u < kSgPullInFlight; u++) {
+        const long long e = e0 + (long long)u * stride;
+        if (e < total) {
+          const int row = (int)e / n4, col4 = (int)e - row * n4;
+          const float *sp = src + (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4;
           asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                       : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(p.Bsrc + off[u]) : "memory");
+                       : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(sp) : "memory");
+        }
       }
 #pragma unroll
-      for (int u = 0; u < 8; u++)
-        if (e0 + u * kStride < total) *reinterpret_cast<float4 *>(const_cast<float *>(p.B) + off[u]) = v[u];
+      for (int u = 0; u < kSgPullInFlight; u++) {
+        const long long e = e0 + (long long)u * stride;
+        if (e < total) {
+          const int row = (int)e / n4, col4 = (int)e - row * n4;
+          *reinterpret_cast<float4 *>(dst + (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4) = v[u];
+        }
+      }
     }
     __threadfence();
     __syncthreads();
@@ -111,16 +118,18 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   const int tid = threadIdx.x;
   int block_id = blockIdx.x;
   if constexpr (PULL) {
-    // roles by order of arrival, so the copy CTAs are running before anything waits for them
+    // Roles by order of arrival: the first n_copy CTAs to start copy B and exit, the others multiply
+    // tile (arrival - n_copy).  A CTA that waits for a panel therefore only ever waits for CTAs that
+    // are already running and that never wait themselves -- no deadlock however few CTAs fit at once.
     __shared__ unsigned int s_slot;
     if (tid == 0) s_slot = atomicAdd(p.pull_ticket, 1u) - p.ticket_base;
     __syncthreads();
-    const unsigned int slot = s_slot;
-    if (slot < (unsigned int)kSgPullCtas) {
-      sgemm_pull_b(p, (int)slot);
+    const int slot = (int)s_slot;
+    if (slot < p.n_copy) {
+      sgemm_pull_b(p, slot);
       return;
     }
-    block_id = (int)slot - kSgPullCtas;
+    block_id = slot - p.n_copy;
   }
   const int lane = tid & 31, warp = tid >> 5;
   const int warp_m = warp >> 2, warp_n = warp & 3;   // 2 x 4 warps
@@ -363,7 +372,7 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
   // split-K when the tiles alone would leave most of the GPU idle (room: 2 CTAs per SM) -- the
   // 64 x 4096 x 64 case of cuda/gemm_fp32.cu:162-258,714-718 and cux's demo shape
   p.splits = 1, p.k_per_split = K > 0 ? K : 1, p.scratch = nullptr, p.tickets = nullptr;
-  p.Bsrc = nullptr, p.pull_ready = nullptr, p.pull_ticket = nullptr, p.ticket_base = 0, p.ready_target = 0, p.panels = 0;
+  p.Bsrc = nullptr, p.pull_ready = nullptr, p.pull_ticket = nullptr, p.ticket_base = 0, p.ready_target = 0, p.panels = 0, p.n_copy = 0;
   const int room = 2 * ctx->sm_count;  // CTAs resident at once
   int splits = 1;
   if (tiles <= 1024 && K >= 256) {
@@ -416,10 +425,13 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
 
 // Row-sharded SGEMM with the broadcast of B fused into the kernel (mpi/alg_matrix_multiply.cpp:52-74:
 // B to every worker, row blocks of A and C).  The root multiplies with b_root in place.  On any other
-// rank the first 64 CTAs of the launch copy B from the root's memory (b_root as mapped into this
-// process) into b_local, 128 rows of B at a time, and every other CTA multiplies, waiting only for the
-// k-panel it is about to load.  Needs the vectorised path: M, N multiples of 128, K of 16, lda/ldb/ldc
-// multiples of 4, 16-byte aligned pointers.
+// rank the first n_copy CTAs to start copy B from the root's memory (b_root as mapped into this
+// process) into b_local, 128 rows of B per readiness flag, and exit; every other CTA multiplies one
+// tile, waiting only for the k-panel it is about to load.  n_copy = the slots the last wave of tiles
+// would leave idle anyway, so that the copy does not push tiles into an extra wave (8192^3: 4096 tiles
+// on 296 slots leave 48), at most 64; 64 when there is no such slack.  Sixteen 16-byte loads in flight
+// per copy thread keep NVLink busy with that few CTAs.  Needs the vectorised path: M, N multiples of
+// 128, K of 16, lda/ldb/ldc multiples of 4, 16-byte aligned pointers.
 CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const float *A,
                                int lda, const float *b_root, float *b_local, int ldb, float beta, float *C,
                                int ldc, int is_root) {
@@ -448,23 +460,28 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
   if (ctx->sg_pull == nullptr) {
     CUXB_CUDA(cudaMalloc((void **)&ctx->sg_pull, (4096 + 32) * sizeof(unsigned int)));
     CUXB_CUDA(cudaMemset(ctx->sg_pull, 0, (4096 + 32) * sizeof(unsigned int)));
-    ctx->sg_pull_calls = 0, ctx->sg_pull_ticket_base = 0, ctx->sg_pull_panels = 0;
+    ctx->sg_pull_calls = 0, ctx->sg_pull_ticket_base = 0, ctx->sg_pull_panels = 0, ctx->sg_pull_ncopy = 0;
   }
-  // the flags only grow, by 64 per call for each of the call's panels: a different panel count would
-  // leave them uneven, so start over from zero when it changes (ordered on the stream)
-  if (ctx->sg_pull_panels != p.panels) {
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int room = 2 * ctx->sm_count;
+  const int spare = (tiles % room) ? room - tiles % room : 0;
+  p.n_copy = (spare >= 16 && spare < 64) ? spare : 64;
+  // the flags only grow, by n_copy per call for each of the call's panels: a different panel count or
+  // n_copy would leave them uneven, so start over from zero when either changes (ordered on the stream)
+  if (ctx->sg_pull_panels != p.panels || ctx->sg_pull_ncopy != p.n_copy) {
     CUXB_CUDA(cudaMemsetAsync(ctx->sg_pull, 0, 4096 * sizeof(unsigned int), st));
     ctx->sg_pull_calls = 0;
     ctx->sg_pull_panels = p.panels;
+    ctx->sg_pull_ncopy = p.n_copy;
   }
-  const unsigned int grid = (unsigned int)(p.tiles_m * p.tiles_n + kSgPullCtas);
+  const unsigned int grid = (unsigned int)(tiles + p.n_copy);
   p.Bsrc = b_root;
   p.pull_ready = ctx->sg_pull;
   p.pull_ticket = ctx->sg_pull + 4096;
   p.ticket_base = ctx->sg_pull_ticket_base;
   ctx->sg_pull_ticket_base += grid;                      // unsigned wrap-around is fine
   ctx->sg_pull_calls++;
-  p.ready_target = ctx->sg_pull_calls * (unsigned int)kSgPullCtas;
+  p.ready_target = ctx->sg_pull_calls * (unsigned int)p.n_copy;
   sgemm_kernel<true, false, true><<<grid, SG_THREADS, 0, st>>>(p);
   CUXB_LAUNCHED();
   return 0;

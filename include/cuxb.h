@@ -163,9 +163,9 @@ int cuxb_mg_scan_i32(cuxb_ctx *ctx, void *stream, long long n, const int32_t *in
 int cuxb_mg_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const void *A,
                              int lda, const void *b_root, void *b_local, int ldb, float beta, void *C, int ldc,
                              int c_dtype, int is_root);
-/* The same for fp32 SGEMM (cfg 3): on a non-root rank the first 64 CTAs of the launch copy B from the
- * root into b_local, 128 rows of B per readiness flag, and the other CTAs multiply, each waiting only for
- * the k-panel it is about to load.  Needs cuxb_sgemm_f32's vectorised shape class (M, N multiples of 128,
+/* The same for fp32 SGEMM (cfg 3): on a non-root rank the first CTAs of the launch to start (16..64 of
+ * them: what the last wave of tiles would leave idle) copy B from the root into b_local, 128 rows of B per
+ * readiness flag, and the other CTAs multiply, each waiting only for the k-panel it is about to load.  Needs cuxb_sgemm_f32's vectorised shape class (M, N multiples of 128,
  * K of 16, leading dimensions multiples of 4, 16-byte aligned pointers), else CUXB_ERR_UNSUPPORTED. */
 int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const float *A, int lda,
                       const float *b_root, float *b_local, int ldb, float beta, float *C, int ldc, int is_root);
