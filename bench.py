@@ -113,7 +113,7 @@ class Workload:
         return self.torch.randint(lo, hi + 1, shape, device="cuda", generator=g, dtype=self.torch.int32).to(dtype)
 
 
-def make_workload(name, torch, ctx, world, rank, dist, peers=None):
+def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"):
     from hpc_b200 import capi, multi
     W = Workload(torch, ctx, world)
     W.collective = "none"
@@ -217,7 +217,12 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None):
         W.kernel = W.step = fn
         if world > 1 and peers is not None:
             # B lives on rank 0 only; every other rank's GEMM kernel pulls it over NVLink while multiplying
-            bsym = peers.symmetric_like(B)
+            # chained: rank r pulls from rank r-1's copy (rank 1 from the root), so every GPU sends B once
+            if bcast == "chain":
+                bsym, b_up = peers.chain(ctx, B)
+            else:                                  # star: everybody pulls from the root (comparison)
+                bsym = peers.symmetric_like(B)
+                b_up = bsym.ptrs[0]
             if rank == 0:
                 bsym.tensor.copy_(B)
             torch.cuda.synchronize()
@@ -225,20 +230,22 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None):
             is_root = rank == 0
             W.step_nccl = fn  # comparison: B already resident on every GPU (no broadcast in the step)
             if name == "hgemm":
-                W.step = lambda: ctx.mg_hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, bsym.ptrs[0], bsym.ptrs[rank], n, 0.0,
+                W.step = lambda: ctx.mg_hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, b_up, bsym.ptrs[rank], n, 0.0,
                                                   C.data_ptr(), n, is_root, capi.FLOAT16, stream())
                 how = "by the otherwise idle warp of every CTA (TMA), column panel by column panel"
             elif name == "sgemm":
-                W.step = lambda: ctx.mg_sgemm_f32(n, n, n, 1.0, A.data_ptr(), n, bsym.ptrs[0], bsym.ptrs[rank], n, 0.0,
+                W.step = lambda: ctx.mg_sgemm_f32(n, n, n, 1.0, A.data_ptr(), n, b_up, bsym.ptrs[rank], n, 0.0,
                                                   C.data_ptr(), n, is_root, stream())
                 how = "by the first 48 CTAs of the launch (the slots its last wave of tiles leaves idle), 128 rows of B per readiness flag"
             else:
-                W.step = lambda: ctx.mg_linear_s8(n, n, n, A.data_ptr(), bsym.ptrs[0], bsym.ptrs[rank], C.data_ptr(),
+                W.step = lambda: ctx.mg_linear_s8(n, n, n, A.data_ptr(), b_up, bsym.ptrs[rank], C.data_ptr(),
                                                   is_root, stream())
                 how = "by the otherwise idle warp of every CTA (TMA), n-block panel by n-block panel"
-            W.collective = ("fused: B (%d MiB) is pulled from rank 0 over NVLink peer memory by the GEMM kernel itself, %s, "
-                            "overlapped with the mainloop (no NCCL launch); rows of C sharded"
-                            % ((B.numel() * B.element_size()) >> 20, how))
+            route = ("from the rank before it (chain: each GPU sends B once)" if bcast == "chain"
+                     else "straight from rank 0 (star)")
+            W.collective = ("fused: B (%d MiB) lives on rank 0; every other rank's GEMM kernel pulls it over NVLink peer "
+                            "memory %s, %s, overlapped with the mainloop (no NCCL launch); rows of C sharded"
+                            % ((B.numel() * B.element_size()) >> 20, route, how))
             W.keep = bsym
         W.units = 2 * n * n * n
         W.unit = "TOP/s" if name == "linear_s8" else "TFLOP/s"
@@ -437,6 +444,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: exchange fused into the kernel over peer memory (default) or a NCCL collective after it")
+    ap.add_argument("--bcast", default="chain", choices=["chain", "star"],
+                    help="N>1 GEMMs: pull B from the previous rank's copy (default) or every rank from the root")
     ap.add_argument("--no-also", action="store_true", help="skip the short passes over the other workloads")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     args = ap.parse_args()
@@ -467,7 +476,7 @@ def main():
             peers = multi.PeerExchange(dist, torch.device("cuda", local))
         except Exception as ex:  # reported in the JSON line, never silent
             peers_note = "peer-memory rendezvous failed (%s): NCCL collective used instead" % str(ex)[:200]
-    W = make_workload(args.workload, torch, ctx, world, rank, dist, peers)
+    W = make_workload(args.workload, torch, ctx, world, rank, dist, peers, args.bcast)
     warmup = max(args.warmup, 3)
 
     # ---- device-resident timing (value)

@@ -12,6 +12,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("CUXB_LIB_PATH") or os.path.join(_HERE, "libcuxb.so")
 
 FLOAT32, INT32, FLOAT16, INT8, BFLOAT16 = 0, 1, 2, 3, 4
+MG_EXCHANGE_BYTES = 256       # CUXB_MG_EXCHANGE_BYTES
+MG_CHAIN_FLAGS_BYTES = 16640  # CUXB_MG_CHAIN_FLAGS_BYTES
 
 
 class CuxbError(RuntimeError):
@@ -66,6 +68,7 @@ SIGNATURES = {
     "cuxb_mg_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i], _i),
     "cuxb_mg_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i], _i),
     "cuxb_mg_linear_s8_s32": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i], _i),
+    "cuxb_mg_set_chain": ([_vp, _vp, _vp, _vp], _i),
     "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
@@ -214,6 +217,10 @@ class Context:
     def mg_linear_s8(self, M, N, K, A, bt_root, bt_local, Cp, is_root, stream=0):
         check(lib().cuxb_mg_linear_s8_s32(self._h, stream, M, N, K, A, bt_root, bt_local, Cp, int(is_root)),
               "cuxb_mg_linear_s8_s32")
+
+    def mg_set_chain(self, flags_local, flags_up, flags_down):
+        check(lib().cuxb_mg_set_chain(self._h, flags_local or None, flags_up or None, flags_down or None),
+              "cuxb_mg_set_chain")
 
     def convert(self, n, src, src_dtype, dst, dst_dtype, stream=0):
         check(lib().cuxb_convert(self._h, stream, n, src, src_dtype, dst, dst_dtype), "cuxb_convert")

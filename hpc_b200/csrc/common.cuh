@@ -76,6 +76,9 @@ struct cuxb_ctx {
   unsigned int *bcast_ready;   // fused B broadcast: per-panel arrival counters (grow by grid size per call)
   unsigned int bcast_calls;
   int bcast_grid, bcast_panels;
+  unsigned int bcast_done_total;   // chained broadcast: panels published so far (all calls)
+  unsigned int *chain_local;       // chained broadcast flags (cuxb_mg_set_chain), peer-mapped
+  const unsigned int *chain_up, *chain_down;
   // sgemm split-K: parked accumulators + per-tile tickets
   void *sg_scratch;
   size_t sg_scratch_bytes;
@@ -83,6 +86,7 @@ struct cuxb_ctx {
   unsigned int *sg_pull;
   unsigned int sg_pull_calls, sg_pull_ticket_base;
   int sg_pull_panels, sg_pull_ncopy;
+  unsigned int sg_pull_done_total;
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];

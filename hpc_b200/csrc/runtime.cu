@@ -201,6 +201,19 @@ CUXB_API int cuxb_enable_peer_access(int device, int peer_device) {
   return 0;
 }
 
+// Chained broadcast for the cuxb_mg_*gemm / cuxb_mg_linear_* calls of this context (see cuxb.h).
+CUXB_API int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *flags_up, const void *flags_down) {
+  CUXB_REQUIRE(ctx != nullptr, CUXB_ERR_INVALID, "cuxb_mg_set_chain: null context");
+  CUXB_REQUIRE(flags_local != nullptr || (flags_up == nullptr && flags_down == nullptr), CUXB_ERR_INVALID,
+               "cuxb_mg_set_chain: flags_up / flags_down given without flags_local");
+  CUXB_REQUIRE((((uintptr_t)flags_local | (uintptr_t)flags_up | (uintptr_t)flags_down) & 3) == 0, CUXB_ERR_INVALID,
+               "cuxb_mg_set_chain: flag buffers must be 4-byte aligned");
+  ctx->chain_local = (unsigned int *)flags_local;
+  ctx->chain_up = (const unsigned int *)flags_up;
+  ctx->chain_down = (const unsigned int *)flags_down;
+  return 0;
+}
+
 CUXB_API int cuxb_stream_create(void **s) {
   CUXB_REQUIRE(s, CUXB_ERR_INVALID, "null");
   cudaStream_t st;

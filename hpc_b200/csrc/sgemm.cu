@@ -55,6 +55,12 @@ struct SgemmArgs {
   unsigned int *pull_ticket;  // arrival ticket, grows by the grid size per call
   unsigned int ticket_base, ready_target;
   int panels, n_copy;
+  // chained broadcast (cuxb_mg_set_chain; the protocol is described in umma_gemm.cu): peer-mapped
+  // flags, one epoch word per panel + the "all panels" word at index 4096
+  unsigned int *chain_local;
+  const unsigned int *chain_up, *chain_down;
+  unsigned int *done_ctr;
+  unsigned int done_target;
 };
 
 constexpr int kSgPullInFlight = 16;  // 16-byte loads in flight per thread: 64 KiB per copy CTA over NVLink
@@ -70,6 +76,16 @@ __device__ __forceinline__ unsigned long long sg_timer_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+__device__ __forceinline__ unsigned int sg_ld_acquire_sys(const unsigned int *p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sg_wait_sys_reached(const unsigned int *p, unsigned int want) {
+  const unsigned long long t0 = sg_timer_ns();
+  while ((int)(sg_ld_acquire_sys(p) - want) < 0)
+    if (sg_timer_ns() - t0 > 20000000000ull) __trap();
+}
 
 // One copy CTA's share of the broadcast: float4 e of a panel (row-major over rows x N/4) belongs to
 // CTA (e / 256) mod n_copy; sixteen loads in flight per thread.
@@ -79,7 +95,20 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
   const int stride = p.n_copy * SG_THREADS;
   const float *src = p.Bsrc;
   float *dst = const_cast<float *>(p.B);
+  unsigned int epoch = 0;
+  if (p.chain_local != nullptr) {
+    // our call epoch; nothing of the previous call may be overwritten before the next rank has read it
+    if (tid == 0) {
+      epoch = sg_ld_acquire_sys(p.chain_local + 4096) + 1;
+      if (p.chain_down != nullptr) sg_wait_sys_reached(p.chain_down + 4096, epoch - 1);
+    }
+    __syncthreads();
+  }
   for (int pnl = 0; pnl < p.panels; pnl++) {
+    if (p.chain_up != nullptr) {
+      if (tid == 0) sg_wait_sys_reached(p.chain_up + pnl, epoch);  // the upstream copy of this panel is complete
+      __syncthreads();
+    }
     const int r0 = pnl * kSgPullPanelK;
     const int rows = min(kSgPullPanelK, p.K - r0);
     const long long total = (long long)rows * n4;  // < 2^31 (checked on the host)
@@ -106,7 +135,17 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
     }
     __threadfence();
     __syncthreads();
-    if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.pull_ready + pnl) : "memory");
+    if (tid == 0) {
+      unsigned int old;
+      asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p.pull_ready + pnl) : "memory");
+      if (p.chain_local != nullptr && old + 1 == p.ready_target) {
+        // last copier of the panel: tell the rank that pulls from us, and count the panel
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_local + pnl), "r"(epoch) : "memory");
+        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p.done_ctr) : "memory");
+        if (old + 1 == p.done_target)
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_local + 4096), "r"(epoch) : "memory");
+      }
+    }
   }
 }
 
@@ -373,6 +412,7 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
   // 64 x 4096 x 64 case of cuda/gemm_fp32.cu:162-258,714-718 and cux's demo shape
   p.splits = 1, p.k_per_split = K > 0 ? K : 1, p.scratch = nullptr, p.tickets = nullptr;
   p.Bsrc = nullptr, p.pull_ready = nullptr, p.pull_ticket = nullptr, p.ticket_base = 0, p.ready_target = 0, p.panels = 0, p.n_copy = 0;
+  p.chain_local = nullptr, p.chain_up = nullptr, p.chain_down = nullptr, p.done_ctr = nullptr, p.done_target = 0;
   const int room = 2 * ctx->sm_count;  // CTAs resident at once
   int splits = 1;
   if (tiles <= 1024 && K >= 256) {
@@ -461,6 +501,7 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
     CUXB_CUDA(cudaMalloc((void **)&ctx->sg_pull, (4096 + 32) * sizeof(unsigned int)));
     CUXB_CUDA(cudaMemset(ctx->sg_pull, 0, (4096 + 32) * sizeof(unsigned int)));
     ctx->sg_pull_calls = 0, ctx->sg_pull_ticket_base = 0, ctx->sg_pull_panels = 0, ctx->sg_pull_ncopy = 0;
+    ctx->sg_pull_done_total = 0;
   }
   const int tiles = p.tiles_m * p.tiles_n;
   const int room = 2 * ctx->sm_count;
@@ -482,6 +523,12 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
   ctx->sg_pull_ticket_base += grid;                      // unsigned wrap-around is fine
   ctx->sg_pull_calls++;
   p.ready_target = ctx->sg_pull_calls * (unsigned int)p.n_copy;
+  p.chain_local = ctx->chain_local, p.chain_up = ctx->chain_up, p.chain_down = ctx->chain_down;
+  p.done_ctr = ctx->sg_pull + 4097, p.done_target = 0;
+  if (ctx->chain_local != nullptr) {
+    ctx->sg_pull_done_total += (unsigned int)p.panels;
+    p.done_target = ctx->sg_pull_done_total;
+  }
   sgemm_kernel<true, false, true><<<grid, SG_THREADS, 0, st>>>(p);
   CUXB_LAUNCHED();
   return 0;

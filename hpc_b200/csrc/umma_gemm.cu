@@ -91,6 +91,25 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int *p
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int *p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned int *p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int atom_add_acq_rel_gpu(unsigned int *p, unsigned int v) {
+  unsigned int old;
+  asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+// spin until *p has reached `want` (wrap-around compare); a peer that never shows up is a launch error
+__device__ __forceinline__ void wait_sys_reached(const unsigned int *p, unsigned int want) {
+  const unsigned long long t0 = global_timer_ns_();
+  while ((int)(ld_acquire_sys_u32(p) - want) < 0)
+    if (global_timer_ns_() - t0 > 20000000000ull) __trap();
+}
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void cluster_sync_all() {
@@ -208,7 +227,17 @@ struct UmmaArgs {
   // once b_ready[p] >= ready_target; the CTA's otherwise idle warp 3 pulls B from the root GPU.
   unsigned int *b_ready;
   unsigned int ready_target;
+  // chained broadcast (cuxb_mg_set_chain): B is pulled from the previous rank's copy instead of the
+  // root's, so every GPU's NVLink egress carries B once however many ranks there are.  Flags live in
+  // peer-mapped memory, one 32-bit word per panel holding the call epoch of the last completed fill,
+  // word kChainDone holding the epoch of the last call whose every panel was filled.
+  unsigned int *chain_local;        // ours (null: no chain)
+  const unsigned int *chain_up;     // the rank we pull from (null: its B is complete -- the root)
+  const unsigned int *chain_down;   // the rank that pulls from us (null: nobody)
+  unsigned int *done_ctr;           // local: panels published, grows by tiles_n per call
+  unsigned int done_target;
 };
+constexpr int kChainDone = 4096;
 
 template <int CG>
 struct UmmaCfg {
@@ -447,13 +476,50 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (B_MN) x = panel * UG_BLOCK_N, y = c * kPullRows;
         else x = (c / kRowBoxes) * 256, y = panel * UG_BLOCK_N + (c % kRowBoxes) * kPullRows;
       };
+      // chain: our call epoch is one more than the last call completed on these flags.  Nothing of
+      // the previous call may be overwritten before the rank that pulls from us has read all of it.
+      unsigned int epoch = 0;
+      if (p.chain_local != nullptr) {
+        epoch = ld_acquire_sys_u32(p.chain_local + kChainDone) + 1;
+        if (p.chain_down != nullptr) wait_sys_reached(p.chain_down + kChainDone, epoch - 1);
+      }
+      int up_known = 0;  // panels of the upstream copy known to be complete
       auto issue = [&](long long i) {
         int panel, x, y;
         coords(i, panel, x, y);
+        if (p.chain_up != nullptr && panel >= up_known) {
+          wait_sys_reached(p.chain_up + panel, epoch);
+          asm volatile("fence.proxy.async;" ::: "memory");
+          up_known = panel + 1;
+        }
         const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
         mbar_expect_tx(bar, kPullBytes);
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                      ::"r"(buf), "l"(&map_bsrc), "r"(bar), "r"(x), "r"(y) : "memory");
+      };
+      // this CTA's share of `panel` is in place: count it; whoever completes the panel tells the next rank
+      // (gpu-scope release per arrival; only the one that completes a panel pays for the sys-scope
+      // store -- its acquire of the counter carries the other CTAs' writes along.  The atomic's result
+      // is looked at one box later (settle), so its round trip to L2 is not on the copy loop's path.)
+      unsigned int pend_old = 0;
+      int pend_panel = -1;
+      auto settle = [&]() {
+        if (pend_panel < 0) return;
+        if (pend_old + 1 == p.ready_target) {
+          st_release_sys_u32(p.chain_local + pend_panel, epoch);
+          if (atom_add_acq_rel_gpu(p.done_ctr, 1u) + 1 == p.done_target)
+            st_release_sys_u32(p.chain_local + kChainDone, epoch);
+        }
+        pend_panel = -1;
+      };
+      auto arrive = [&](int panel) {
+        if (p.chain_local == nullptr) {
+          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.b_ready + panel) : "memory");
+          return;
+        }
+        settle();
+        pend_old = atom_add_acq_rel_gpu(p.b_ready + panel, 1u);
+        pend_panel = panel;
       };
       if (total > 0) issue(0);
       if (total > 1) issue(1);
@@ -462,6 +528,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         coords(i, panel, x, y);
         const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
         mbar_wait(bar, (uint32_t)((i >> 1) & 1));
+        settle();
         asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                      ::"l"(&map_bdst), "r"(buf), "r"(x), "r"(y) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -470,7 +537,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // every store of this panel is complete
           asm volatile("fence.proxy.async;" ::: "memory");
           __threadfence();
-          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.b_ready + panel) : "memory");
+          arrive(panel);
         }
         if (i + 2 < total) {
           if (!last_of_panel) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging buffer free again
@@ -479,8 +546,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
       // CTAs that own no box of a panel still have to be counted
       if (mine_per_panel == 0)
-        for (int panel = 0; panel < p.tiles_n; panel++)
-          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.b_ready + panel) : "memory");
+        for (int panel = 0; panel < p.tiles_n; panel++) arrive(panel);
+      settle();
     }
     __syncwarp();
   } else if (warp >= 4) {
@@ -614,6 +681,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   p.tiles_n = (int)div_up(N, UG_BLOCK_N);
   p.k_blocks = (int)div_up(K, kBlockK);
   p.b_ready = nullptr, p.ready_target = 0;
+  p.chain_local = nullptr, p.chain_up = nullptr, p.chain_down = nullptr, p.done_ctr = nullptr, p.done_target = 0;
   const int total = p.tiles_m * p.tiles_n;
   int clusters = ctx->sm_count / CG;
   if (clusters > total) clusters = total;
@@ -629,8 +697,9 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
     rc = make_map(ctx, &mdst, B, ebytes, dt, rows, cols, (uint64_t)ldb, 256, box_rows, false);
     if (rc) return rc;
     if (ctx->bcast_ready == nullptr) {
-      CUXB_CUDA(cudaMalloc((void **)&ctx->bcast_ready, 4096 * sizeof(unsigned int)));
-      CUXB_CUDA(cudaMemset(ctx->bcast_ready, 0, 4096 * sizeof(unsigned int)));
+      CUXB_CUDA(cudaMalloc((void **)&ctx->bcast_ready, (4096 + 32) * sizeof(unsigned int)));
+      CUXB_CUDA(cudaMemset(ctx->bcast_ready, 0, (4096 + 32) * sizeof(unsigned int)));
+      ctx->bcast_done_total = 0;
       ctx->bcast_calls = 0;
       ctx->bcast_grid = 0;
       ctx->bcast_panels = 0;
@@ -646,6 +715,12 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
     ctx->bcast_calls++;
     p.b_ready = ctx->bcast_ready;
     p.ready_target = ctx->bcast_calls * (unsigned int)(clusters * CG);
+    if (ctx->chain_local != nullptr) {
+      p.chain_local = ctx->chain_local, p.chain_up = ctx->chain_up, p.chain_down = ctx->chain_down;
+      p.done_ctr = ctx->bcast_ready + 4096;  // beyond the panel counters, never reset
+      ctx->bcast_done_total += (unsigned int)p.tiles_n;
+      p.done_target = ctx->bcast_done_total;
+    }
   }
 
   auto kern = umma_gemm_kernel<KIND, B_MN, CT, CG>;

@@ -93,3 +93,21 @@ class PeerExchange:
         out.handle = symm.rendezvous(out.tensor, dist.group.WORLD)
         out.ptrs = [int(p) for p in out.handle.buffer_ptrs]
         return out
+
+    def chain(self, ctx, b_like):
+        """Set up the chained broadcast (cuxb_mg_set_chain) for ctx: a symmetric copy of B and symmetric
+        flags; rank r pulls from rank r - 1.  Returns (bsym, upstream_ptr): bsym.tensor is this rank's B
+        (the root fills it), upstream_ptr the B to pass as b_root / bt_root."""
+        import torch
+        import torch.distributed as dist
+        from . import capi
+        bsym = self.symmetric_like(b_like)
+        fsym = self.symmetric_like(torch.empty(capi.MG_CHAIN_FLAGS_BYTES // 4, dtype=torch.int32, device=b_like.device))
+        fsym.tensor.zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        r, w = self.rank, self.world
+        if r > 0 and w > 2:   # with two ranks the chain is the star: no flags needed
+            ctx.mg_set_chain(fsym.ptrs[r], fsym.ptrs[r - 1] if r >= 2 else 0, fsym.ptrs[r + 1] if r + 1 < w else 0)
+        bsym.flags = fsym
+        return bsym, (bsym.ptrs[r - 1] if r > 0 else bsym.ptrs[0])

@@ -173,6 +173,19 @@ int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float al
  * (256 rows of Bt) by n-block panel.  Same requirements as cuxb_linear_s8_s32. */
 int cuxb_mg_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, int K, const int8_t *A,
                           const int8_t *bt_root, int8_t *bt_local, int32_t *C, int is_root);
+/* Chained broadcast.  By default every non-root rank pulls B straight from the root, whose NVLink egress
+ * then carries B (world - 1) times -- fine at 2 GPUs, the bottleneck at 8.  After cuxb_mg_set_chain the
+ * b_root / bt_root argument of the calls above means "the copy of B on the rank I pull from" (rank r pulls
+ * from rank r - 1's b_local, rank 1 from the root), so that every GPU sends B once.  The flag buffers are
+ * peer-mapped device memory of CUXB_MG_CHAIN_FLAGS_BYTES, zeroed once before the first call:
+ * flags_local = this rank's; flags_up = that of the rank pulled from (NULL when that rank is the root: its
+ * B is complete); flags_down = that of the rank that pulls from this one (NULL for the last rank).  A panel
+ * is pulled once the upstream flags say it has landed there, and a call does not overwrite b_local before
+ * the downstream rank has read all of the previous call's.  All non-root ranks must make the same
+ * sequence of chained calls.  Host-side state only: takes effect for later calls; NULL, NULL, NULL
+ * switches back to pulling from the root. */
+#define CUXB_MG_CHAIN_FLAGS_BYTES 16640
+int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *flags_up, const void *flags_down);
 int cuxb_enable_peer_access(int device, int peer_device);
 
 /* ---- GEMM: C = alpha * A[M,K] * B[K,N] + beta * C, row-major.

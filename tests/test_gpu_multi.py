@@ -172,3 +172,55 @@ def test_fused_b_broadcast_sgemm_and_int8_two_gpus():
         assert np.array_equal(dBt_local.cpu().numpy(), Bt)
         for r in range(world):
             assert np.array_equal(dC8[r].cpu().numpy(), oracle.linear_s8(A8[r], Bt, threads=8)), "rank %d rep %d" % (r, rep)
+
+
+def test_chained_broadcast_across_two_gpus():
+    """cuxb_mg_set_chain with links that really wait: the root's B is on GPU 0, 'rank 1' (GPU 1) pulls it,
+    'rank 2' (a second context on GPU 0) pulls rank 1's copy from GPU 1 panel by panel as it lands there."""
+    world = 2
+    ctxs, _, _ = _setup(world)
+    c1, c2 = ctxs[1], capi.Context(0)
+    nflag = capi.MG_CHAIN_FLAGS_BYTES // 4
+    f1 = torch.zeros(nflag, dtype=torch.int32, device="cuda:1")
+    f2 = torch.zeros(nflag, dtype=torch.int32, device="cuda:0")
+    g0 = torch.Generator(device="cuda:0")
+    g0.manual_seed(3)
+    for kind in ("f16", "f32"):
+        if kind == "f16":
+            M, N, K = 1024, 2304, 2000
+            mk = lambda shape, lo, hi: torch.randint(lo, hi, shape, device="cuda:0", generator=g0).half()
+            A0, B0 = mk((M, K), -10, 10), mk((K, N), -10, 10)
+            plain = lambda c, A, B, C: c.hgemm_f16(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), N, 0.0, C.data_ptr(), N, capi.FLOAT16)
+            mg = lambda c, A, Bup, Bl, C: c.mg_hgemm_f16(M, N, K, 1.0, A.data_ptr(), K, Bup.data_ptr(), Bl.data_ptr(), N, 0.0,
+                                                         C.data_ptr(), N, False)
+        else:
+            M, N, K = 1024, 1152, 528
+            mk = lambda shape, lo, hi: torch.randint(lo, hi, shape, device="cuda:0", generator=g0).float()
+            A0, B0 = mk((M, K), -2, 6), mk((K, N), -2, 6)
+            plain = lambda c, A, B, C: c.sgemm_f32(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), N, 0.0, C.data_ptr(), N)
+            mg = lambda c, A, Bup, Bl, C: c.mg_sgemm_f32(M, N, K, 1.0, A.data_ptr(), K, Bup.data_ptr(), Bl.data_ptr(), N, 0.0,
+                                                         C.data_ptr(), N, False)
+        A1 = A0.to("cuda:1")
+        want = torch.zeros((M, N), dtype=A0.dtype, device="cuda:0")
+        plain(ctxs[0], A0, B0, want)
+        B1, C1 = torch.zeros_like(B0, device="cuda:1"), torch.zeros_like(want, device="cuda:1")
+        B2, C2 = torch.zeros_like(B0), torch.zeros_like(want)
+        # load the pulling instantiations on both devices before any launch waits on the other GPU
+        mg(c1, A1, B1, B1.clone(), C1)
+        mg(c2, A0, B0, B2, C2)
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        c1.mg_set_chain(f1.data_ptr(), 0, f2.data_ptr())
+        c2.mg_set_chain(f2.data_ptr(), f1.data_ptr(), 0)
+        for rep in range(3):
+            B1.zero_(), B2.zero_(), C1.zero_(), C2.zero_()
+            for r in range(world):
+                torch.cuda.synchronize(r)
+            mg(c1, A1, B0, B1, C1)     # GPU 1 pulls from the root on GPU 0
+            mg(c2, A0, B1, B2, C2)     # GPU 0 pulls from GPU 1's copy while it is being filled
+            for r in range(world):
+                torch.cuda.synchronize(r)
+            assert torch.equal(B1.cpu(), B0.cpu()) and torch.equal(B2, B0), (kind, rep)
+            assert torch.equal(C1.cpu(), want.cpu()) and torch.equal(C2, want), (kind, rep)
+        c1.mg_set_chain(0, 0, 0)
+        c2.mg_set_chain(0, 0, 0)

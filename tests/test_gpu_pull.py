@@ -142,3 +142,69 @@ def test_pull_flags_survive_a_change_of_panel_count():
                            1280, False)
         sync()
         assert torch.equal(Bl, B) and torch.equal(got, want), Kf
+
+
+def test_chained_broadcast_flag_protocol_sequential():
+    """cuxb_mg_set_chain on one GPU: 'rank 1' pulls from the root's B, 'rank 2' from rank 1's copy.  The
+    two launches run one after the other on the default stream, so nothing ever spins here -- this checks the
+    epoch arithmetic (panel flags, the all-panels word, the wait for the downstream rank's previous call)
+    over repeated calls and changing shapes; tests/test_gpu_multi.py runs a chain whose links really wait."""
+    c1, c2 = capi.Context(0), capi.Context(0)
+    nflag = capi.MG_CHAIN_FLAGS_BYTES // 4
+    f1 = torch.zeros(nflag, dtype=torch.int32, device="cuda")
+    f2 = torch.zeros(nflag, dtype=torch.int32, device="cuda")
+    c1.mg_set_chain(f1.data_ptr(), 0, f2.data_ptr())
+    c2.mg_set_chain(f2.data_ptr(), f1.data_ptr(), 0)
+    g = torch.Generator(device="cuda")
+    g.manual_seed(11)
+    epoch = 0
+    for (M, N, K) in [(512, 1280, 520), (512, 768, 256), (512, 1280, 520)]:
+        A = torch.randint(-10, 10, (M, K), device="cuda", generator=g).half()
+        for rep in range(2):
+            B = torch.randint(-10, 10, (K, N), device="cuda", generator=g).half()
+            want = torch.zeros((M, N), dtype=torch.float16, device="cuda")
+            ctx().hgemm_f16(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), N, 0.0, want.data_ptr(), N, capi.FLOAT16)
+            B1, B2 = torch.zeros_like(B), torch.zeros_like(B)
+            C1, C2 = torch.zeros_like(want), torch.zeros_like(want)
+            sync()
+            c1.mg_hgemm_f16(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), B1.data_ptr(), N, 0.0, C1.data_ptr(), N, False)
+            c2.mg_hgemm_f16(M, N, K, 1.0, A.data_ptr(), K, B1.data_ptr(), B2.data_ptr(), N, 0.0, C2.data_ptr(), N, False)
+            sync()
+            epoch += 1
+            assert torch.equal(B1, B) and torch.equal(B2, B)
+            assert torch.equal(C1, want) and torch.equal(C2, want)
+            panels = (N + 255) // 256
+            for f in (f1, f2):
+                fl = f.cpu().numpy()
+                assert np.all(fl[:panels] == epoch) and fl[4096] == epoch
+    # the same flags carry on through the fp32 and int8 kernels (one epoch sequence per chain)
+    M, N, K = 384, 256, 272
+    A = torch.randint(-2, 6, (M, K), device="cuda", generator=g).float()
+    B = torch.randint(-2, 6, (K, N), device="cuda", generator=g).float()
+    want = torch.zeros((M, N), device="cuda")
+    ctx().sgemm_f32(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), N, 0.0, want.data_ptr(), N)
+    for rep in range(2):
+        B1, B2, C1, C2 = torch.zeros_like(B), torch.zeros_like(B), torch.zeros_like(want), torch.zeros_like(want)
+        sync()
+        c1.mg_sgemm_f32(M, N, K, 1.0, A.data_ptr(), K, B.data_ptr(), B1.data_ptr(), N, 0.0, C1.data_ptr(), N, False)
+        c2.mg_sgemm_f32(M, N, K, 1.0, A.data_ptr(), K, B1.data_ptr(), B2.data_ptr(), N, 0.0, C2.data_ptr(), N, False)
+        sync()
+        epoch += 1
+        assert torch.equal(B2, B) and torch.equal(C1, want) and torch.equal(C2, want)
+        assert int(f1[4096]) == epoch and int(f2[4096]) == epoch and int(f2[2]) == epoch  # 3 k-panels
+    A8 = torch.randint(-128, 128, (256, 512), device="cuda", generator=g, dtype=torch.int32).to(torch.int8)
+    Bt = torch.randint(-128, 128, (600, 512), device="cuda", generator=g, dtype=torch.int32).to(torch.int8)
+    want = torch.zeros((256, 600), dtype=torch.int32, device="cuda")
+    ctx().linear_s8(256, 600, 512, A8.data_ptr(), Bt.data_ptr(), want.data_ptr())
+    B1, B2 = torch.zeros_like(Bt), torch.zeros_like(Bt)
+    C1, C2 = torch.zeros_like(want), torch.zeros_like(want)
+    sync()
+    c1.mg_linear_s8(256, 600, 512, A8.data_ptr(), Bt.data_ptr(), B1.data_ptr(), C1.data_ptr(), False)
+    c2.mg_linear_s8(256, 600, 512, A8.data_ptr(), B1.data_ptr(), B2.data_ptr(), C2.data_ptr(), False)
+    sync()
+    assert torch.equal(B2, Bt) and torch.equal(C1, want) and torch.equal(C2, want)
+    assert int(f2[4096]) == epoch + 1
+    c1.mg_set_chain(0, 0, 0)
+    c2.mg_set_chain(0, 0, 0)
+    with pytest.raises(capi.CuxbError):
+        c1.mg_set_chain(0, f1.data_ptr(), 0)
