@@ -74,6 +74,8 @@ def ref():
     R.ref_cux_gemm.argtypes = [_i, _i, _i, _i, _f, _f32p, _i, _f32p, _i, _f, _f32p, _i]
     R.ref_cux_dot_v0.argtypes = [_i, _f32p, _f32p, _f32p]
     R.ref_cux_nrm2_v0.argtypes = [_i, _f32p, _f32p]
+    if hasattr(R, "ref_std_dot_mt"):
+        R.ref_std_dot_mt.argtypes = [_i, _f32p, _f32p, _i, _f32p]
     R.ref_reduce_host.argtypes = [_f32p, _f32p, _i]
     R.ref_hgemm_host.argtypes = [_i, _i, _i, _u16p, _i, _u16p, _i, _u16p, _i]
     R.ref_omp_gemm.argtypes = [_i, _i, _i, _i, _f, _f32p, _i, _f32p, _i, _f32p, _i]

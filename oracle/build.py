@@ -82,6 +82,9 @@ def build_ref(force=False):
           "-mavx512vnni", "-mavx512bf16", "-I" + REF]),
         ("simd/x86/vector_scan.cpp", "ref_scan_main", ["-std=c++17", "-mavx2"]),
         ("openmp/alg_matrix_multiply.cpp", "ref_ompmm_main", ["-std=c++14"]),
+        # the sample relies on MSVC's headers for memset / clock: supply them on the command line
+        ("std/alg_vector_dot_product.cpp", "ref_stddot_main",
+         ["-std=c++14", "-pthread", "-include", "cstring", "-include", "ctime"]),
     ]:
         obj = os.path.join(OUT, os.path.basename(rel) + ".o")
         run(["g++"] + common + extra + ["-Dmain=" + main, "-c", os.path.join(REF, rel), "-o", obj])
@@ -90,7 +93,7 @@ def build_ref(force=False):
     run(["g++", "-std=c++14", "-mavx2", "-mfma"] + common +
         ["-I" + OUT, "-I" + CUDA_INC, "-c", shim, "-o", obj])
     objs.append(obj)
-    run(["g++", "-shared", "-fopenmp", "-o", so] + objs)
+    run(["g++", "-shared", "-fopenmp", "-pthread", "-o", so] + objs)
     # keep only the library: intermediates (objects, extracted line ranges) are removed
     for f in os.listdir(OUT):
         if f.endswith(".o") or f.endswith(".inc"):

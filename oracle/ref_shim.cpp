@@ -50,6 +50,9 @@ void MatrixMulSerial(const int M, const int N, const int K, const float ALPHA, c
 void MatrixMulMP(const int M, const int N, const int K, const float ALPHA, const float *A,
                  const int lda, const float *B, const int ldb, float *C, const int ldc);
 
+// std/alg_vector_dot_product.cpp (main -> ref_stddot_main): the reference's all-cores dot product
+void DotProductMTv1(float *src0, float *src1, int len, int num_threads, float *dst);
+
 #define REF_API extern "C" __attribute__((visibility("default")))
 
 REF_API int ref_cpu_has_avx512(void) {
@@ -71,6 +74,15 @@ REF_API int ref_cux_gemm(int version, int M, int N, int K, float alpha, const fl
     case 5: cuxref::GemmHostV5(M, N, K, alpha, A, lda, B, ldb, beta, C, ldc); return 0;
   }
   return -1;
+}
+// DotProductMTv1 (std/alg_vector_dot_product.cpp:19-56): one std::thread per slice, partials added in
+// slice order.  The sample clears num_threads floats at dst (:28), so dst gets that much room here.
+REF_API void ref_std_dot_mt(int len, const float *a, const float *b, int num_threads, float *res) {
+  if (num_threads < 1) num_threads = 1;
+  float *dst = (float *)calloc((size_t)num_threads + 1, sizeof(float));
+  DotProductMTv1(const_cast<float *>(a), const_cast<float *>(b), len, num_threads, dst);
+  *res = dst[0];
+  free(dst);
 }
 REF_API void ref_cux_dot_v0(int len, const float *a, const float *b, float *res) {
   cuxref::DotHostV0(len, a, b, res);

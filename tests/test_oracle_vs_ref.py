@@ -160,3 +160,19 @@ def test_scan_i32_wraparound_matches_numpy():
     assert np.array_equal(got, want)
     assert got.min() < 0  # it really wrapped
     assert oracle.sum_i32(x) == want[-1] - 5
+
+
+def test_reference_all_cores_dot_matches_the_serial_one_on_integer_fills():
+    """std/alg_vector_dot_product.cpp:19-56 (DotProductMTv1, timed by bench.py beside DotHostV0): with the
+    cux integer fill every partial sum is exact, so slicing the vector over threads cannot change the result."""
+    R = oracle.ref()
+    if R is None or not hasattr(R, "ref_std_dot_mt"):
+        pytest.skip("oracle/_ref not built with the std/ sample")
+    rng = np.random.default_rng(3)
+    for n in (1, 7, 1000, 123457):
+        a = rng.integers(-2, 3, size=n).astype(np.float32)
+        b = rng.integers(-2, 3, size=n).astype(np.float32)
+        for th in (1, 3, 8):
+            out = np.zeros(1, np.float32)
+            R.ref_std_dot_mt(n, a, b, th, out)
+            assert out[0] == oracle.dot_f32(a, b), (n, th)
