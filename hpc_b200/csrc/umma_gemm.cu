@@ -484,14 +484,19 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (p.chain_down != nullptr) wait_sys_reached(p.chain_down + kChainDone, epoch - 1);
       }
       int up_known = 0;  // panels of the upstream copy known to be complete
+      // The upstream flag lives on another GPU: a look at it is an NVLink round trip.  The copy loop
+      // therefore asks for the panel of box i + 2 BEFORE it sits down to wait for box i (whose own
+      // load is a round trip of the same length), so the two overlap.
+      auto need_up = [&](int panel) {
+        if (p.chain_up == nullptr || panel < up_known) return;
+        wait_sys_reached(p.chain_up + panel, epoch);
+        asm volatile("fence.proxy.async;" ::: "memory");
+        up_known = panel + 1;
+      };
       auto issue = [&](long long i) {
         int panel, x, y;
         coords(i, panel, x, y);
-        if (p.chain_up != nullptr && panel >= up_known) {
-          wait_sys_reached(p.chain_up + panel, epoch);
-          asm volatile("fence.proxy.async;" ::: "memory");
-          up_known = panel + 1;
-        }
+        need_up(panel);
         const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
         mbar_expect_tx(bar, kPullBytes);
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -527,6 +532,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         int panel, x, y;
         coords(i, panel, x, y);
         const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
+        if (i + 2 < total) need_up((int)((i + 2) / mine_per_panel));
         mbar_wait(bar, (uint32_t)((i >> 1) & 1));
         settle();
         asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
