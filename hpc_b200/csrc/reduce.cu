@@ -258,6 +258,13 @@ static int reduce_entry(const char *name, cuxb_ctx *ctx, void *stream, long long
   }
   CUXB_REQUIRE(n == 0 || (a != nullptr && (OP != OP_DOT || b != nullptr)), CUXB_ERR_INVALID,
                "%s: input pointer is null", name);
+  if (mg.world > 1) {
+    // every rank makes the same sequence of mg calls, so the counters agree; drawn only here, after
+    // the argument checks, so that a rejected call does not put this rank one epoch ahead
+    ctx->mg_epoch = ctx->mg_epoch + 1;
+    if (ctx->mg_epoch == 0) ctx->mg_epoch = 1;
+    mg.epoch = ctx->mg_epoch;
+  }
   return launch_reduce<OP, T>(ctx, st, n, a, b, res, finish_sqrt, ctx->red_partials,
                               ctx->red_ticket, reduce_grid(ctx, n), mg);
 }
@@ -303,10 +310,7 @@ int mg_prepare(const char *name, cuxb_ctx *ctx, int world, int rank, void *const
                  "%s: peer buffer %d is null or not 8-byte aligned", name, r);
     mg->peer[r] = (unsigned long long *)peer_bufs[r];
   }
-  ctx->mg_epoch = ctx->mg_epoch + 1;
-  if (ctx->mg_epoch == 0) ctx->mg_epoch = 1;
-  mg->epoch = ctx->mg_epoch;
-  return 0;
+  return 0;  // the epoch is drawn in reduce_entry, once nothing can fail any more
 }
 }  // namespace cuxb
 

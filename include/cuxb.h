@@ -22,6 +22,17 @@
  *     them (0-frameworks/cux/src/operator/gemm.cpp:458-463: lda=K, ldb=N, ldc=N).
  *   - kernels never fall back to the CPU.  A missing device, a non-sm_100
  *     device or an unsupported shape is an error.
+ *   - concurrency: a context owns one set of workspaces (block partials and
+ *     tickets, scan tile states, split-K scratch, broadcast flags), so the
+ *     kernel entry points of ONE context must be issued in stream order -- one
+ *     stream at a time, or streams the caller has ordered with events.  This
+ *     is cux's own model (one OpAssistor, default stream,
+ *     0-frameworks/cux/include/executor.h:74-103).  Work that is meant to
+ *     overlap on several streams uses one context per stream; contexts are
+ *     cheap (a few KiB of device memory until a workspace is first needed).
+ *     Calls may come from any host thread, but not from two at once for the
+ *     same context, except the *_host entry points, which serialise
+ *     themselves.
  */
 #ifndef CUXB_H_
 #define CUXB_H_
