@@ -154,7 +154,17 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
         W.metric = "reduce HBM GB/s (fp32 %s, N=2^28 per GPU)" % ("dot-product" if name == "dot" else name)
         W.result = res
         W.launches_per_step = 1
-        W.host_inputs = lambda: [a, b] if b is not None else [a]
+
+        def make_e2e():
+            pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t)
+            ha, hb = pin(a), (pin(b) if b is not None else None)
+            hres = torch.zeros(1, dtype=torch.float32, pin_memory=True)
+            call = {"dot": lambda: ctx.dot_f32_host(n, ha.data_ptr(), hb.data_ptr(), hres.data_ptr()),
+                    "sum": lambda: ctx.sum_f32_host(n, ha.data_ptr(), hres.data_ptr()),
+                    "nrm2": lambda: ctx.nrm2_f32_host(n, ha.data_ptr(), hres.data_ptr())}[name]
+            return {"call": call, "h2d": W.units, "d2h": 4, "api": "cuxb_%s_f32_host" % name, "result": hres,
+                    "combine": None if name == "nrm2" else "sum", "keep": (ha, hb)}
+        W.make_e2e = make_e2e
     elif name == "scan":
         n = N_SCAN
         x = W.gen_int((n,), -2, 2, torch.int32, seed)
@@ -185,6 +195,13 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
         W.desc = "int32 inclusive scan N=2^30 per GPU (configs[4]); 8 GiB moved per GPU > L2"
         W.metric = "scan HBM GB/s (int32 inclusive prefix scan, N=2^30 per GPU)"
         W.result = out[-1:]
+
+        def make_e2e():
+            hx = torch.empty(n, dtype=torch.int32, pin_memory=True).copy_(x)
+            hout = torch.empty(n, dtype=torch.int32, pin_memory=True)
+            return {"call": lambda: ctx.scan_i32_host(n, hx.data_ptr(), hout.data_ptr(), 0), "h2d": 4 * n, "d2h": 4 * n,
+                    "api": "cuxb_scan_i32_host", "result": hout[-1:], "combine": None, "keep": (hx, hout)}
+        W.make_e2e = make_e2e if world == 1 else None   # sharded e2e would need the seed exchange on the host
     elif name in ("sgemm", "hgemm", "linear_s8"):
         if name == "sgemm":
             n = SGEMM_N
@@ -247,6 +264,22 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
                             "memory %s, %s, overlapped with the mainloop (no NCCL launch); rows of C sharded"
                             % ((B.numel() * B.element_size()) >> 20, route, how))
             W.keep = bsym
+
+        def make_e2e():
+            pin = lambda t: torch.empty(t.shape, dtype=t.dtype, pin_memory=True).copy_(t)
+            hA, hB = pin(A), pin(B)
+            hC = torch.empty(C.shape, dtype=C.dtype, pin_memory=True)
+            if name == "sgemm":
+                call = lambda: ctx.sgemm_f32_host(n, n, n, 1.0, hA.data_ptr(), n, hB.data_ptr(), n, 0.0, hC.data_ptr(), n)
+            elif name == "hgemm":
+                call = lambda: ctx.hgemm_f16_host(n, n, n, 1.0, hA.data_ptr(), n, hB.data_ptr(), n, 0.0, hC.data_ptr(), n,
+                                                  capi.FLOAT16)
+            else:
+                call = lambda: ctx.linear_s8_host(n, n, n, hA.data_ptr(), hB.data_ptr(), hC.data_ptr())
+            api = {"sgemm": "cuxb_sgemm_f32_host", "hgemm": "cuxb_hgemm_f16_f32acc_host", "linear_s8": "cuxb_linear_s8_s32_host"}[name]
+            return {"call": call, "h2d": (A.numel() + B.numel()) * A.element_size(), "d2h": C.numel() * C.element_size(),
+                    "api": api, "result": hC[-1, -1:], "combine": None, "keep": (hA, hB, hC)}
+        W.make_e2e = make_e2e
         W.units = 2 * n * n * n
         W.unit = "TOP/s" if name == "linear_s8" else "TFLOP/s"
         W.bound = "tensor" if name != "sgemm" else "ffma"
@@ -528,24 +561,17 @@ def main():
 
     # ---- end to end through the host-buffer C ABI (pinned host memory, H2D + kernel + D2H per step)
     e2e = None
-    if args.workload == "dot":
-        n = N_DOT
-        ha = torch.empty(n, dtype=torch.float32, pin_memory=True)
-        hb = torch.empty(n, dtype=torch.float32, pin_memory=True)
-        ins = W.host_inputs()
-        ha.copy_(ins[0])
-        hb.copy_(ins[1])
-        hres = torch.zeros(1, dtype=torch.float32, pin_memory=True)
+    if getattr(W, "make_e2e", None) is not None:
+        E = W.make_e2e()
         part = torch.zeros(1, device="cuda")
 
         def e2e_step():
-            ctx.dot_f32_host(n, ha.data_ptr(), hb.data_ptr(), hres.data_ptr())
-            if world > 1:
-                part.copy_(hres, non_blocking=True)
+            E["call"]()                                  # H2D of the inputs, kernel, D2H of the result: blocking
+            if world > 1 and E["combine"] == "sum":      # the scalar of every rank, combined like the device path
+                part.copy_(E["result"], non_blocking=True)
                 dist.all_reduce(part)
-                hres.copy_(part)
-        e2e_steps = max(3, min(args.steps, 10))
-        t_w0 = time.perf_counter()
+                E["result"].copy_(part)
+        e2e_steps = max(3, min(args.steps, 10 if W.bound == "hbm" else 5))
         for _ in range(2):
             e2e_step()
         torch.cuda.synchronize()
@@ -559,10 +585,12 @@ def main():
         if dist is not None:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e_ms = float(dt[0]) * 1e3 / e2e_steps
-        e2e = {"value": rate(W.units * world, e2e_ms, "GB/s"), "unit": "GB/s", "h2d_bytes_per_step": 8 * n,
-               "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms, "steps": e2e_steps,
-               "api": "cuxb_dot_f32_host (pinned host vectors; host wall clock around the blocking call)",
-               "result": float(hres[0]), "device_result": float(W.result[0])}
+        e2e = {"value": rate(W.units * world, e2e_ms, W.unit), "unit": W.unit, "h2d_bytes_per_step": int(E["h2d"]),
+               "d2h_bytes_per_step": int(E["d2h"]), "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "api": "%s (pinned host buffers; host wall clock around the blocking call%s)" % (
+                   E["api"], "; + one all-reduce of the scalar" if world > 1 and E["combine"] else ""),
+               "result": float(E["result"][0])}
+        del E
 
     # ---- short passes over the other configs (N=1 only)
     also = {}

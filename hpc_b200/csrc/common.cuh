@@ -48,6 +48,7 @@ static inline long long div_up(long long a, long long b) { return (a + b - 1) / 
 constexpr int kScanTileElems = 8192;                 // 512 threads x 16 ints
 constexpr long long kScanMaxTiles = (1ll << 31) / kScanTileElems;  // n < 2^31 (cux uses int lengths)
 constexpr int kReduceMaxBlocks = 2048;
+constexpr int kHostMaxChunks = 16;  // *_host entry points: at most this many row / element chunks in flight
 
 // A cuTensorMapEncodeTiled result, keyed by everything that went into it.
 struct TmaCacheEntry {
@@ -90,7 +91,12 @@ struct cuxb_ctx {
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];
-  cudaStream_t stage_stream;
+  cudaStream_t stage_stream;   // the *_host entry points launch their kernels here
+  // *_host pipelines: uploads and downloads run on their own streams so that PCIe carries both
+  // directions while the kernels of earlier chunks run; events order chunk i's upload -> kernel -> download
+  cudaStream_t up_stream, down_stream;
+  cudaEvent_t ev_up[cuxb::kHostMaxChunks + 1], ev_k[cuxb::kHostMaxChunks];
+  bool host_pipe_ready;
   // TMA descriptor cache
   cuxb::TmaCacheEntry tma_cache[16];  // most recent TMA descriptors (encoding one costs microseconds)
   int tma_cache_n;

@@ -100,6 +100,12 @@ CUXB_API int cuxb_ctx_destroy(cuxb_ctx *c) {
   for (int i = 0; i < 4; i++)
     if (c->stage[i]) cudaFree(c->stage[i]);
   if (c->stage_stream) cudaStreamDestroy(c->stage_stream);
+  if (c->host_pipe_ready) {
+    cudaStreamDestroy(c->up_stream);
+    cudaStreamDestroy(c->down_stream);
+    for (int i = 0; i <= kHostMaxChunks; i++) cudaEventDestroy(c->ev_up[i]);
+    for (int i = 0; i < kHostMaxChunks; i++) cudaEventDestroy(c->ev_k[i]);
+  }
   delete c->mu;
   delete c->tma_mu;
   delete c;

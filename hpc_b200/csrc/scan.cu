@@ -419,6 +419,13 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
                         (unsigned int)tiles);
 }
 
+// for host_api.cu: a scan whose seed is `seed` plus (when seed_ptr != null) an int32 read on the device
+int scan_i32_device_seed(cuxb_ctx *ctx, cudaStream_t st, long long n, const int32_t *in, int32_t *out, int32_t seed,
+                         const int32_t *seed_ptr) {
+  return scan_entry<unsigned int>("cuxb_scan_i32_host", ctx, (void *)st, n, (const unsigned int *)in,
+                                  (unsigned int *)out, (unsigned int)seed, (const unsigned int *)seed_ptr);
+}
+
 const void *scan_kernel_symbol() { return (const void *)scan_kernel<unsigned int>; }
 int scan_smem_bytes() { return kScanSmemBytes; }
 

@@ -250,7 +250,12 @@ int cuxb_fill_random(cuxb_ctx *ctx, void *stream, long long n, void *dst, int dt
 
 /* ---- host-buffer entry points: what a cux plugin that is handed HOST arrays
  * calls.  Inputs are copied host->device, the kernel runs, the result is
- * copied back and the call returns after the stream has drained.  Pinned host
+ * copied back and the call returns after the context's streams have drained.
+ * The GEMMs and the scan, which send back as much as they take in, run as a
+ * pipeline once more than 32 MiB is moved: row (element) chunks, chunk i+1
+ * uploading while chunk i is computed and chunk i-1 downloads, on three streams
+ * (16384^3 fp16: 33.8 -> 22.5 ms, the upload of A and B alone is 19.5 ms).  The
+ * result is bit-identical to one kernel over the whole problem.  Pinned host
  * memory (cuxb_malloc_host) makes the copies asynchronous DMA; pageable memory
  * works but is slower.  Device staging buffers are owned by ctx and reused. */
 int cuxb_dot_f32_host(cuxb_ctx *ctx, long long n, const float *a, const float *b, float *res);

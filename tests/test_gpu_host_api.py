@@ -129,3 +129,55 @@ def test_device_random_fill_is_a_pure_function_of_seed_and_index():
     sync()
     g = host(d)
     assert g.min() >= 0 and g.max() < 3 and np.allclose(g * 100, np.round(g * 100), atol=1e-3)
+
+
+def test_host_pipelines_cut_into_chunks_match_the_device_kernels():
+    """Above 32 MiB of traffic the GEMM / scan host entry points become three-stream pipelines (upload of
+    chunk i+1, kernel of chunk i, download of chunk i-1).  Same bits as one kernel over device-resident
+    data, with padded leading dimensions, beta != 0 (C travels both ways) and a ragged last chunk."""
+    c = ctx()
+    # ---- fp32, beta != 0, padded rows
+    M, N, K = 4224, 1024, 1024   # 33 tile-rows: the last chunk is smaller
+    lda, ldb, ldc = K + 8, N + 4, N + 12
+    A = np.zeros((M, lda), np.float32); A[:, :K] = dg.int_fill((M, K), -2, 5, tag=41)
+    B = np.zeros((K, ldb), np.float32); B[:, :N] = dg.int_fill((K, N), -2, 5, tag=42)
+    C = np.full((M, ldc), 9.0, np.float32); C[:, :N] = dg.int_fill((M, N), -2, 5, tag=43)
+    dA, dB, dC = dev(A[:, :K].copy()), dev(B[:, :N].copy()), dev(C[:, :N].copy())
+    c.sgemm_f32(M, N, K, 2.0, dA.data_ptr(), K, dB.data_ptr(), N, -1.0, dC.data_ptr(), N)
+    sync()
+    out = C.copy()
+    c.sgemm_f32_host(M, N, K, 2.0, p(A), lda, p(B), ldb, -1.0, p(out), ldc)
+    assert np.array_equal(out[:, :N], host(dC))
+    assert np.all(out[:, N:] == 9.0)                      # the padding of C is left alone
+    # ---- fp16 -> fp16
+    M, N, K = 8192, 2048, 1024
+    A16 = oracle.f32_to_f16(dg.int_fill((M, K), -10, 9, tag=44))
+    B16 = oracle.f32_to_f16(dg.int_fill((K, N), -10, 9, tag=45))
+    dA, dB = dev(A16), dev(B16)
+    dC = torch.zeros((M, N), dtype=torch.int16, device="cuda")
+    c.hgemm_f16(M, N, K, 1.0, dA.data_ptr(), K, dB.data_ptr(), N, 0.0, dC.data_ptr(), N, capi.FLOAT16)
+    sync()
+    out16 = np.zeros((M, N), np.uint16)
+    c.hgemm_f16_host(M, N, K, 1.0, p(A16), K, p(B16), N, 0.0, p(out16), N, capi.FLOAT16)
+    assert np.array_equal(out16, host(dC, np.uint16))
+    # ---- int8 -> int32 (bit-exact against the oracle on sampled rows as well)
+    M, N, K = 4352, 2048, 1024
+    A8 = dg.int_fill((M, K), -128, 127, tag=46).astype(np.int8)
+    Bt = dg.int_fill((N, K), -128, 127, tag=47).astype(np.int8)
+    out32 = np.zeros((M, N), np.int32)
+    c.linear_s8_host(M, N, K, p(A8), p(Bt), p(out32))
+    rows = [0, 1, 255, 256, 2047, 2048, 4095, 4351]
+    assert np.array_equal(out32[rows], oracle.linear_s8(A8[rows], Bt, threads=8))
+    dA, dB = dev(A8), dev(Bt)
+    dC = torch.zeros((M, N), dtype=torch.int32, device="cuda")
+    c.linear_s8(M, N, K, dA.data_ptr(), dB.data_ptr(), dC.data_ptr())
+    sync()
+    assert np.array_equal(out32, host(dC))
+    # ---- int32 scan: chunk i continues from chunk i-1's last output, wrap-around included
+    n = 6_000_011
+    x = np.full(n, 3000, np.int32)
+    x[::7] = -11
+    out = np.empty_like(x)
+    c.scan_i32_host(n, p(x), p(out), -5)
+    want = oracle.scan_i32(x, -5)
+    assert want.min() < 0 and np.array_equal(out, want)
