@@ -68,6 +68,8 @@ SIGNATURES = {
     "cuxb_mg_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i, _i], _i),
     "cuxb_mg_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _vp, _i, _f, _vp, _i, _i], _i),
     "cuxb_mg_linear_s8_s32": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i], _i),
+    "cuxb_mg_linear_bf16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i], _i),
+    "cuxb_mg_linear_f16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i], _i),
     "cuxb_mg_set_chain": ([_vp, _vp, _vp, _vp], _i),
     "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
@@ -217,6 +219,10 @@ class Context:
     def mg_linear_s8(self, M, N, K, A, bt_root, bt_local, Cp, is_root, stream=0):
         check(lib().cuxb_mg_linear_s8_s32(self._h, stream, M, N, K, A, bt_root, bt_local, Cp, int(is_root)),
               "cuxb_mg_linear_s8_s32")
+
+    def mg_linear_16(self, kind, M, N, K, A, bt_root, bt_local, Cp, c_dtype, is_root, stream=0):
+        f = {"bf16": lib().cuxb_mg_linear_bf16_f32acc, "f16": lib().cuxb_mg_linear_f16_f32acc}[kind]
+        check(f(self._h, stream, M, N, K, A, bt_root, bt_local, Cp, c_dtype, int(is_root)), "cuxb_mg_linear_%s_f32acc" % kind)
 
     def mg_set_chain(self, flags_local, flags_up, flags_down):
         check(lib().cuxb_mg_set_chain(self._h, flags_local or None, flags_up or None, flags_down or None),

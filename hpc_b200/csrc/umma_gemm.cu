@@ -888,3 +888,35 @@ CUXB_API int cuxb_mg_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, in
   return launch_umma<KIND_S8, false, CUXB_INT32, 2>(ctx, (cudaStream_t)stream, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N,
                                                     pull);
 }
+
+// The same for the 16-bit linears (linear.cpp:137-182's layout): Bt[N,K] pulled in 256-k x 16-row boxes.
+CUXB_API int cuxb_mg_linear_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A,
+                                        const void *bt_root, void *bt_local, void *C, int c_dtype, int is_root) {
+  CUXB_REQUIRE(c_dtype == CUXB_BFLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,
+               "cuxb_mg_linear_bf16_f32acc: c_dtype must be CUXB_BFLOAT16 or CUXB_FLOAT32");
+  const void *Bt = is_root ? bt_root : (const void *)bt_local;
+  int rc = check_common("cuxb_mg_linear_bf16_f32acc", ctx, M, N, K, A, Bt, C, 2, K, K, N, c_dtype == CUXB_BFLOAT16 ? 2 : 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  CUXB_REQUIRE(bt_root != nullptr && ((uintptr_t)bt_root & 15) == 0, CUXB_ERR_INVALID,
+               "cuxb_mg_linear_bf16_f32acc: bt_root is null or not 16-byte aligned");
+  const void *pull = is_root ? nullptr : bt_root;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c_dtype == CUXB_BFLOAT16)
+    return launch_umma<KIND_BF16, false, CUXB_BFLOAT16, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
+  return launch_umma<KIND_BF16, false, CUXB_FLOAT32, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
+}
+CUXB_API int cuxb_mg_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A,
+                                       const void *bt_root, void *bt_local, void *C, int c_dtype, int is_root) {
+  CUXB_REQUIRE(c_dtype == CUXB_FLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,
+               "cuxb_mg_linear_f16_f32acc: c_dtype must be CUXB_FLOAT16 or CUXB_FLOAT32");
+  const void *Bt = is_root ? bt_root : (const void *)bt_local;
+  int rc = check_common("cuxb_mg_linear_f16_f32acc", ctx, M, N, K, A, Bt, C, 2, K, K, N, c_dtype == CUXB_FLOAT16 ? 2 : 4);
+  if (rc) return rc < 0 ? 0 : rc;
+  CUXB_REQUIRE(bt_root != nullptr && ((uintptr_t)bt_root & 15) == 0, CUXB_ERR_INVALID,
+               "cuxb_mg_linear_f16_f32acc: bt_root is null or not 16-byte aligned");
+  const void *pull = is_root ? nullptr : bt_root;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c_dtype == CUXB_FLOAT16)
+    return launch_umma<KIND_F16, false, CUXB_FLOAT16, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
+  return launch_umma<KIND_F16, false, CUXB_FLOAT32, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
+}

@@ -184,6 +184,11 @@ int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, float al
  * (256 rows of Bt) by n-block panel.  Same requirements as cuxb_linear_s8_s32. */
 int cuxb_mg_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, int K, const int8_t *A,
                           const int8_t *bt_root, int8_t *bt_local, int32_t *C, int is_root);
+/* The 16-bit linears (LinearNormalBf16, linear.cpp:137-151, and its fp16 twin) the same way. */
+int cuxb_mg_linear_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A, const void *bt_root,
+                               void *bt_local, void *C, int c_dtype, int is_root);
+int cuxb_mg_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A, const void *bt_root,
+                              void *bt_local, void *C, int c_dtype, int is_root);
 /* Chained broadcast.  By default every non-root rank pulls B straight from the root, whose NVLink egress
  * then carries B (world - 1) times -- fine at 2 GPUs, the bottleneck at 8.  After cuxb_mg_set_chain the
  * b_root / bt_root argument of the calls above means "the copy of B on the rank I pull from" (rank r pulls

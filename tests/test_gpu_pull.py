@@ -208,3 +208,29 @@ def test_chained_broadcast_flag_protocol_sequential():
     c2.mg_set_chain(0, 0, 0)
     with pytest.raises(capi.CuxbError):
         c1.mg_set_chain(0, f1.data_ptr(), 0)
+
+
+@pytest.mark.parametrize("kind", ["bf16", "f16"])
+def test_linear_16bit_pull_bit_exact(kind):
+    """K-major 16-bit Bt pulled in 256-k x 16-row boxes; integer fills, so bit-exact vs the plain kernel and,
+    for bf16, vs LinearNormalBf16 (linear.cpp:137-151)."""
+    M, N, K = 384, 1096, 1096   # ragged N and K (multiples of 8 only: 16-byte row pitches)
+    A = dg.int_fill((M, K), -4, 4, tag=51)
+    Bt = dg.int_fill((N, K), -4, 4, tag=52)
+    cvt = oracle.f32_to_bf16 if kind == "bf16" else oracle.f32_to_f16
+    A16, B16 = cvt(A), cvt(Bt)
+    dt = capi.BFLOAT16 if kind == "bf16" else capi.FLOAT16
+    dA, dBroot = dev(A16), dev(B16)
+    want = torch.zeros((M, N), dtype=torch.int16, device="cuda")
+    (ctx().linear_bf16 if kind == "bf16" else ctx().linear_f16)(M, N, K, dA.data_ptr(), dBroot.data_ptr(), want.data_ptr(), dt)
+    sync()
+    if kind == "bf16":
+        assert np.array_equal(host(want, np.uint16), oracle.linear_bf16(A16, B16, threads=8))
+    for rep in range(2):
+        dBloc = torch.zeros((N, K), dtype=torch.int16, device="cuda")
+        dC = torch.zeros((M, N), dtype=torch.int16, device="cuda")
+        sync()
+        ctx().mg_linear_16(kind, M, N, K, dA.data_ptr(), dBroot.data_ptr(), dBloc.data_ptr(), dC.data_ptr(), dt, False)
+        sync()
+        assert np.array_equal(host(dBloc, np.uint16), B16)
+        assert torch.equal(dC, want)
