@@ -16,7 +16,10 @@
 // value(32) | epoch(30) | status(2) share one word, so a single 64-bit
 // load observes a consistent (status, value) pair and the words never need
 // clearing between launches: a word from an older launch has a stale epoch and
-// reads as "not ready".
+// reads as "not ready".  The epoch itself lives in DEVICE memory next to the state
+// words: every CTA reads it when it starts and the last CTA to finish (a ticket)
+// advances it, so a launch recorded into a CUDA graph gets a fresh epoch on every
+// replay -- nothing about a launch's protocol state is baked into its arguments.
 //
 // Scratch memory: 8 bytes per tile (1 KiB per Mi elements), owned by the
 // cuxb_ctx.  Launches that share a ctx must not overlap.
@@ -44,6 +47,10 @@ __device__ __forceinline__ unsigned long long ld_state(const unsigned long long 
 }
 __device__ __forceinline__ void st_state(unsigned long long *p, unsigned long long v) {
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// launch number -> epoch in [1, 2^30 - 1]: never 0, which is what zero-filled scratch holds
+__device__ __forceinline__ unsigned int scan_epoch_of(unsigned long long launches_done) {
+  return (unsigned int)(launches_done % 0x3fffffffull) + 1u;
 }
 
 template <typename T> __device__ __forceinline__ unsigned int to_bits(T v);
@@ -207,7 +214,10 @@ constexpr int kScanSmemBytes = kScanRing * kScanTileElems * 4;  // 192 KiB
 template <typename T>
 __global__ void __launch_bounds__(kScanCtaThreads, 1)
 scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed_ptr,
-            unsigned long long *__restrict__ state, unsigned int epoch, unsigned int num_tiles) {
+            unsigned long long *__restrict__ state, unsigned long long *ctl, unsigned int num_tiles) {
+  // ctl[0]: launches completed on this scratch, ctl[1]: ticket of CTAs that have finished this launch
+  const unsigned long long launches_done = ld_state(ctl);
+  const unsigned int epoch = scan_epoch_of(launches_done);
   if (seed_ptr != nullptr) seed += *seed_ptr;  // sharded scan: the exclusive offset computed on the device
   typedef typename V4<T>::type V;
   extern __shared__ __align__(16) unsigned char scan_smem[];
@@ -355,15 +365,33 @@ scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed
     const int q = passes - d;
     if (q >= 0) finish_tile(q, q % kScanRing);
   }
+  // This CTA's helper warp settled its last tile before the store above could run, so the CTA no
+  // longer reads anybody's state words.  The last CTA through here opens the next epoch.
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(ctl + 1, 1ull) == (unsigned long long)gridDim.x - 1) {
+      st_state(ctl + 1, 0ull);
+      __threadfence();
+      st_state(ctl, launches_done + 1);
+    }
+  }
 }
 
 // The CTAs of one scan wait on each other's aggregates, so they must all be resident at once.  A
 // cooperative launch makes the driver guarantee that (or refuse): two scans issued on different
 // streams are then run one after the other instead of interleaving into a dead wait.
 template <typename T>
-static int launch_scan(cudaStream_t st, unsigned int grid, const T *in, T *out, long long n, T seed, const T *seed_ptr,
-                       unsigned long long *state, unsigned int epoch, unsigned int tiles) {
-  CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
+static int launch_scan(int device, cudaStream_t st, unsigned int grid, const T *in, T *out, long long n, T seed,
+                       const T *seed_ptr, unsigned long long *state, unsigned long long *ctl, unsigned int tiles) {
+  {
+    // once per instantiation and device (the attribute call costs about a microsecond of host time)
+    static std::atomic<unsigned long long> smem_set{0};
+    const unsigned long long bit = 1ull << (device & 63);
+    if (!(smem_set.load(std::memory_order_acquire) & bit)) {
+      CUXB_CUDA(cudaFuncSetAttribute(scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kScanSmemBytes));
+      smem_set.fetch_or(bit, std::memory_order_release);
+    }
+  }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid, 1, 1);
@@ -375,7 +403,7 @@ static int launch_scan(cudaStream_t st, unsigned int grid, const T *in, T *out, 
   attr[0].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  CUXB_CUDA(cudaLaunchKernelEx(&cfg, scan_kernel<T>, in, out, n, seed, seed_ptr, state, epoch, tiles));
+  CUXB_CUDA(cudaLaunchKernelEx(&cfg, scan_kernel<T>, in, out, n, seed, seed_ptr, state, ctl, tiles));
   g_launches.fetch_add(1);
   return 0;
 }
@@ -403,20 +431,22 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
       ctx->scan_state = nullptr;
       ctx->scan_state_tiles = 0;
     }
-    CUXB_CUDA(cudaMalloc((void **)&ctx->scan_state, cap * sizeof(unsigned long long)));
-    CUXB_CUDA(cudaMemset(ctx->scan_state, 0, cap * sizeof(unsigned long long)));
+    // state words + 32 control words (launch counter, finish ticket), all zero: launch 0 uses epoch 1
+    CUXB_CUDA(cudaMalloc((void **)&ctx->scan_state, (cap + 32) * sizeof(unsigned long long)));
+    CUXB_CUDA(cudaMemset(ctx->scan_state, 0, (cap + 32) * sizeof(unsigned long long)));
     ctx->scan_state_tiles = cap;
+    ctx->scan_epoch = 0;
   }
-  ctx->scan_epoch = (ctx->scan_epoch + 1) & 0x3fffffffu;
-  if (ctx->scan_epoch == 0) {
-    // 2^30 launches later the epoch wraps: clear the words once and skip 0
+  // The device-side epoch repeats after 2^30 - 1 launches.  A word that old can only survive in a
+  // tile slot no launch has touched since; wipe the words every 2^29 calls so it cannot be mistaken
+  // for a fresh one (graph replays do not pass through here: see cuxb.h).
+  ctx->scan_epoch = (ctx->scan_epoch + 1) & 0x1fffffffu;
+  if (ctx->scan_epoch == 0)
     CUXB_CUDA(cudaMemsetAsync(ctx->scan_state, 0, ctx->scan_state_tiles * sizeof(unsigned long long), st));
-    ctx->scan_epoch = 1;
-  }
   long long grid = (long long)ctx->sm_count * kScanCtasPerSM;  // all CTAs resident (see scan_kernel)
   if (grid > tiles) grid = tiles;
-  return launch_scan<T>(st, (unsigned int)grid, in, out, n, seed, seed_ptr, ctx->scan_state, ctx->scan_epoch,
-                        (unsigned int)tiles);
+  return launch_scan<T>(ctx->device, st, (unsigned int)grid, in, out, n, seed, seed_ptr, ctx->scan_state,
+                        ctx->scan_state + ctx->scan_state_tiles, (unsigned int)tiles);
 }
 
 // for host_api.cu: a scan whose seed is `seed` plus (when seed_ptr != null) an int32 read on the device
@@ -445,7 +475,7 @@ int scan_smem_bytes() { return kScanSmemBytes; }
 constexpr long long kNoAllocMaxElems = 1ll << 26;  // 67,108,864 int32 values = 256 MiB of input
 constexpr int kNoAllocMaxTiles = (int)(kNoAllocMaxElems / 4096);  // 16384 words = 128 KiB
 static_assert(kScanTileElems >= 4096, "the static scratch is sized for tiles of at least 4096 elements");
-constexpr int kNoAllocCounterWords = 32;  // 256 bytes after the state words; [0],[1] are used
+constexpr int kNoAllocCounterWords = 32;  // 256 bytes after the state words: [0] launch counter, [1] finish ticket
 static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + kNoAllocCounterWords];
 
 // Host-side bookkeeping, one slot per device ordinal.  `scratch` is the DEVICE address of
@@ -503,23 +533,22 @@ CUXB_API int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in,
     CUXB_REQUIRE(ptr != nullptr, CUXB_ERR_UNSUPPORTED, "cuxb_scan_i32_noalloc: static scratch has no device address");
     CUXB_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
     d.scratch = ptr;
-    d.epoch = 0;   // the array starts zero-filled, and no launch ever uses epoch 0
+    d.epoch = 0;   // host-side call counter (only for the periodic wipe below)
     d.ready = true;
   }
   // The array still holds whatever the previous call left.  Nothing has to be cleared for that:
-  // every state word carries the epoch of the launch that wrote it, this launch gets a fresh epoch,
-  // and a word with any other epoch reads as "not published yet".  Only when the 30-bit epoch wraps
-  // are the words wiped (on the caller's stream, ahead of the kernel).
-  d.epoch = (d.epoch + 1) & 0x3fffffffu;
-  if (d.epoch == 0) {  // epoch wrapped after 2^30 calls: wipe the state words once and skip 0
+  // every state word carries the epoch of the launch that wrote it, every launch runs under a fresh
+  // epoch (counted on the device, in the word after the state words), and a word with any other
+  // epoch reads as "not published yet".  Only every 2^29 calls are the words wiped (on the caller's
+  // stream, ahead of the kernel), long before an epoch value could come round again.
+  d.epoch = (d.epoch + 1) & 0x1fffffffu;
+  if (d.epoch == 0)
     CUXB_CUDA(cudaMemsetAsync(d.scratch, 0, (size_t)kNoAllocMaxTiles * sizeof(unsigned long long), st));
-    d.epoch = 1;
-  }
   const unsigned int tiles = (unsigned int)div_up(n, kScanTileElems);
   unsigned int grid = (unsigned int)d.sm_count * kScanCtasPerSM;  // every CTA resident at once
   if (grid > tiles) grid = tiles;
-  return launch_scan<unsigned int>(st, grid, (const unsigned int *)in, (unsigned int *)out, n, (unsigned int)seed,
-                                   (const unsigned int *)nullptr, d.scratch, d.epoch, tiles);
+  return launch_scan<unsigned int>(dev, st, grid, (const unsigned int *)in, (unsigned int *)out, n, (unsigned int)seed,
+                                   (const unsigned int *)nullptr, d.scratch, d.scratch + kNoAllocMaxTiles, tiles);
 }
 
 // Sharded scan across GPUs (rank r holds the r-th contiguous slice): one reduction kernel whose

@@ -730,7 +730,15 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   }
 
   auto kern = umma_gemm_kernel<KIND, B_MN, CT, CG>;
-  CUXB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  {
+    // once per instantiation and device (the attribute call costs about a microsecond of host time)
+    static std::atomic<unsigned long long> smem_set{0};
+    const unsigned long long bit = 1ull << (ctx->device & 63);
+    if (!(smem_set.load(std::memory_order_acquire) & bit)) {
+      CUXB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+      smem_set.fetch_or(bit, std::memory_order_release);
+    }
+  }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(clusters * CG, 1, 1);

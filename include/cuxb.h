@@ -33,6 +33,15 @@
  *     Calls may come from any host thread, but not from two at once for the
  *     same context, except the *_host entry points, which serialise
  *     themselves.
+ *   - CUDA graphs: the single-GPU kernel entry points (reductions, scans
+ *     including cuxb_scan_i32_noalloc, GEMMs, linears, convert, fill) may be
+ *     recorded by stream capture and replayed: no protocol state is baked
+ *     into a launch's arguments (the scan counts its epoch on the device, the
+ *     reduction and split-K tickets reset themselves).  Call once outside the
+ *     capture first, so that workspaces exist and nothing allocates while
+ *     capturing.  NOT capturable: the *_host entry points (they synchronise)
+ *     and the cuxb_mg_* entry points (their epochs and flag targets are
+ *     counted on the host, once per call).
  */
 #ifndef CUXB_H_
 #define CUXB_H_
