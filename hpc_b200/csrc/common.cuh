@@ -72,7 +72,7 @@ struct cuxb_ctx {
   unsigned long long *scan_state;
   long long scan_state_tiles;
   unsigned int scan_epoch;
-  unsigned int mg_epoch;       // multi-GPU exchange epoch (all ranks make the same sequence of mg calls)
+  unsigned int mg_epoch;       // unused (the exchange epoch lives in the exchange buffer, on the device)
   int *mg_seed;                // device int32: the sharded scan's exclusive offset
   unsigned int *bcast_ready;   // fused B broadcast: per-panel arrival counters (grow by grid size per call)
   unsigned int bcast_calls;

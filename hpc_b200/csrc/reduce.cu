@@ -48,9 +48,11 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4 *p) {
 // every rank and adds them up in rank order -- so all ranks get the same, order-fixed result without
 // a separate collective launch.  Slots alternate with the epoch's parity: a rank that runs one call
 // ahead writes the other half, and it cannot run two ahead because it needs everybody's word first.
+// The epoch is a call counter kept in the rank's OWN exchange buffer (word 16; only this warp ever
+// touches it), so every rank counts the same sequence without the host -- and a call recorded into
+// a CUDA graph runs under a fresh epoch on every replay.
 struct MgExchange {
   int world, rank;              // world <= 1: single GPU, no exchange
-  unsigned int epoch;           // identical on every rank for this call, never 0
   int mode;                     // 0: sum over all ranks   1: exclusive prefix (sum of the lower ranks)
   unsigned long long *peer[8];  // peer[r] = rank r's exchange buffer (>= CUXB_MG_EXCHANGE_BYTES)
 };
@@ -78,24 +80,30 @@ template <> __device__ __forceinline__ unsigned int of_bits<unsigned int>(unsign
 template <typename T>
 __device__ __forceinline__ T mg_exchange(const MgExchange &mg, T mine) {
   const int lane = threadIdx.x & 31;
-  const int slot = (mg.epoch & 1) * 8;
-  const unsigned long long word = ((unsigned long long)bits_of<T>(mine) << 32) | mg.epoch;
   unsigned long long *dst = nullptr, *own = nullptr;
 #pragma unroll
   for (int r = 0; r < 8; r++) {
     if (r == lane) dst = mg.peer[r];
     if (r == mg.rank) own = mg.peer[r];
   }
+  unsigned long long calls = 0;                       // exchanges completed on this buffer
+  if (lane == 0) calls = ld_sys_u64(own + 16);
+  calls = __shfl_sync(0xffffffffu, calls, 0);
+  const unsigned int epoch = (unsigned int)(calls % 0xffffffffull) + 1u;   // never 0 (zeroed buffers)
+  const int slot = (int)(calls & 1) * 8;   // strict alternation (the epoch's own parity repeats once at its wrap)
+  const unsigned long long word = ((unsigned long long)bits_of<T>(mine) << 32) | epoch;
   if (lane < mg.world) st_sys_u64(dst + slot + mg.rank, word);
   unsigned long long w = 0;
   if (lane < mg.world) {
     const unsigned long long t0 = global_timer_ns();
     while (true) {
       w = ld_sys_u64(own + slot + lane);
-      if ((unsigned int)w == mg.epoch) break;
+      if ((unsigned int)w == epoch) break;
       if (global_timer_ns() - t0 > 20000000000ull) __trap();  // a rank never arrived: fail, do not hang
     }
   }
+  __syncwarp();
+  if (lane == 0) st_sys_u64(own + 16, calls + 1);   // everybody's word for this call has been read
   const T val = (lane < mg.world) ? of_bits<T>((unsigned int)(w >> 32)) : (T)0;
   T total = 0;
   for (int r = 0; r < mg.world; r++) {  // rank order: every rank adds in the same order
@@ -258,13 +266,6 @@ static int reduce_entry(const char *name, cuxb_ctx *ctx, void *stream, long long
   }
   CUXB_REQUIRE(n == 0 || (a != nullptr && (OP != OP_DOT || b != nullptr)), CUXB_ERR_INVALID,
                "%s: input pointer is null", name);
-  if (mg.world > 1) {
-    // every rank makes the same sequence of mg calls, so the counters agree; drawn only here, after
-    // the argument checks, so that a rejected call does not put this rank one epoch ahead
-    ctx->mg_epoch = ctx->mg_epoch + 1;
-    if (ctx->mg_epoch == 0) ctx->mg_epoch = 1;
-    mg.epoch = ctx->mg_epoch;
-  }
   return launch_reduce<OP, T>(ctx, st, n, a, b, res, finish_sqrt, ctx->red_partials,
                               ctx->red_ticket, reduce_grid(ctx, n), mg);
 }
@@ -310,7 +311,7 @@ int mg_prepare(const char *name, cuxb_ctx *ctx, int world, int rank, void *const
                  "%s: peer buffer %d is null or not 8-byte aligned", name, r);
     mg->peer[r] = (unsigned long long *)peer_bufs[r];
   }
-  return 0;  // the epoch is drawn in reduce_entry, once nothing can fail any more
+  return 0;
 }
 }  // namespace cuxb
 

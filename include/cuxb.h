@@ -39,9 +39,11 @@
  *     into a launch's arguments (the scan counts its epoch on the device, the
  *     reduction and split-K tickets reset themselves).  Call once outside the
  *     capture first, so that workspaces exist and nothing allocates while
- *     capturing.  NOT capturable: the *_host entry points (they synchronise)
- *     and the cuxb_mg_* entry points (their epochs and flag targets are
- *     counted on the host, once per call).
+ *     capturing.  The multi-GPU reductions and scan (cuxb_mg_dot_f32 ...
+ *     cuxb_mg_scan_i32) can be captured too: their exchange epoch is counted
+ *     in the exchange buffer.  NOT capturable: the *_host entry points (they
+ *     synchronise) and the fused-broadcast GEMMs (cuxb_mg_*gemm*,
+ *     cuxb_mg_linear_*: their flag targets are counted on the host, per call).
  */
 #ifndef CUXB_H_
 #define CUXB_H_

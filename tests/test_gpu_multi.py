@@ -224,3 +224,51 @@ def test_chained_broadcast_across_two_gpus():
             assert torch.equal(C1.cpu(), want.cpu()) and torch.equal(C2, want), (kind, rep)
         c1.mg_set_chain(0, 0, 0)
         c2.mg_set_chain(0, 0, 0)
+
+
+def test_fused_exchange_replayed_from_cuda_graphs():
+    """One graph per GPU, each holding that rank's mg_dot + mg_scan; replayed together on fresh data.  The
+    exchange epoch is counted in the exchange buffer, so every replay runs under a new one."""
+    world = 2
+    ctxs, bufs, ptrs = _setup(world)
+    n = 500_003
+    da = [torch.zeros(n, device="cuda:%d" % r) for r in range(world)]
+    db = [torch.zeros(n, device="cuda:%d" % r) for r in range(world)]
+    dx = [torch.zeros(n, dtype=torch.int32, device="cuda:%d" % r) for r in range(world)]
+    res = [torch.zeros(1, device="cuda:%d" % r) for r in range(world)]
+    out = [torch.zeros_like(t) for t in dx]
+    streams = [torch.cuda.Stream(device=r) for r in range(world)]
+
+    def work(r, st):
+        ctxs[r].mg_dot_f32(n, da[r].data_ptr(), db[r].data_ptr(), res[r].data_ptr(), world, r, ptrs, st)
+        ctxs[r].mg_scan_i32(n, dx[r].data_ptr(), out[r].data_ptr(), world, r, ptrs, st)
+    # warm-up: both ranks must run it together (they wait for each other)
+    for r in range(world):
+        with torch.cuda.device(r):
+            work(r, streams[r].cuda_stream)
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    graphs = []
+    for r in range(world):
+        with torch.cuda.device(r):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=streams[r]):
+                work(r, torch.cuda.current_stream().cuda_stream)
+            graphs.append(g)
+    for rep in range(3):
+        a = [dg.int_fill(n, -2, 2, tag=300 + 10 * rep + r) for r in range(world)]
+        b = [dg.int_fill(n, -2, 2, tag=350 + 10 * rep + r) for r in range(world)]
+        x = [dg.int_fill(n, -5, 5, np.int32, tag=400 + 10 * rep + r) for r in range(world)]
+        for r in range(world):
+            da[r].copy_(torch.from_numpy(a[r])), db[r].copy_(torch.from_numpy(b[r])), dx[r].copy_(torch.from_numpy(x[r]))
+            torch.cuda.synchronize(r)
+        for r in range(world):
+            with torch.cuda.device(r):
+                graphs[r].replay()
+        for r in range(world):
+            torch.cuda.synchronize(r)
+        want_dot = oracle.dot_f32(np.concatenate(a), np.concatenate(b))
+        want_scan = oracle.scan_i32(np.concatenate(x))
+        for r in range(world):
+            assert float(res[r][0]) == float(want_dot), (rep, r)
+        assert np.array_equal(np.concatenate([o.cpu().numpy() for o in out]), want_scan), rep
