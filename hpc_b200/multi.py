@@ -5,8 +5,9 @@ Only what the hot path needs (north_star):
   * int32 scan: per-GPU totals exchanged, every rank seeds its local scan with
     the sum of the lower ranks' totals (what MPI_Exscan does in the reference's
     mpi/base_reduce_alltoall_scan.cpp:101)                                       -> scan_seed
-  * GEMM / linear: rows of A and C sharded, B replicated (the decomposition of
-    mpi/alg_matrix_multiply.cpp:52-67); no collective on the data path           -> shard_rows
+  * GEMM / linear: rows of A and C sharded (the decomposition of
+    mpi/alg_matrix_multiply.cpp:52-67); B lives on rank 0 and is pulled by the
+    GEMM kernels themselves, rank to rank                                        -> shard_rows, chain_plan
 The functions take tensors on whatever device the process group's backend serves (cuda for nccl,
 cpu for gloo), so the same code is exercised by the world_size-2 gloo tests on CPU.
 """
@@ -22,6 +23,19 @@ def shard_range(n, world, rank):
 
 def shard_rows(M, world, rank):
     return shard_range(M, world, rank)
+
+
+def chain_plan(world, rank, mode="chain"):
+    """Who pulls B from whom in the fused broadcast.  Returns (source, flags_up, flags_down) as ranks
+    (None = not applicable): `source` is the rank whose copy of B this rank's kernel reads, `flags_up` the
+    rank whose readiness flags it polls (None when the source is the root, whose B is complete),
+    `flags_down` the rank that pulls from this one and must finish a call before the next overwrites B.
+    mode "star": everybody pulls from rank 0 and nobody needs flags.  The root never pulls."""
+    if rank == 0 or world == 1:
+        return None, None, None
+    if mode == "star" or world == 2:
+        return 0, None, None
+    return rank - 1, (rank - 1 if rank >= 2 else None), (rank + 1 if rank + 1 < world else None)
 
 
 def allreduce_sum(dist, partial):
@@ -107,7 +121,9 @@ class PeerExchange:
         torch.cuda.synchronize()
         dist.barrier()
         r, w = self.rank, self.world
+        src, up, down = chain_plan(w, r)
         if r > 0 and w > 2:   # with two ranks the chain is the star: no flags needed
-            ctx.mg_set_chain(fsym.ptrs[r], fsym.ptrs[r - 1] if r >= 2 else 0, fsym.ptrs[r + 1] if r + 1 < w else 0)
+            ctx.mg_set_chain(fsym.ptrs[r], fsym.ptrs[up] if up is not None else 0,
+                             fsym.ptrs[down] if down is not None else 0)
         bsym.flags = fsym
-        return bsym, (bsym.ptrs[r - 1] if r > 0 else bsym.ptrs[0])
+        return bsym, bsym.ptrs[src if src is not None else 0]

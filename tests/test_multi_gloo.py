@@ -93,3 +93,26 @@ def test_shard_range_partitions_exactly():
             sizes = [hi - lo for lo, hi in spans]
             assert max(sizes) - min(sizes) <= 1
     assert multi.wrap_i32(2 ** 31) == -2 ** 31 and multi.wrap_i32(-2 ** 31 - 1) == 2 ** 31 - 1
+
+
+def test_chain_plan_is_a_single_path_from_the_root():
+    """Fused broadcast routing (hpc_b200.multi.chain_plan): every non-root rank has exactly one source, the
+    sources form one chain rooted at rank 0, and up/down flag partners are each other's mirror image."""
+    for world in range(1, 9):
+        plans = [multi.chain_plan(world, r) for r in range(world)]
+        assert plans[0] == (None, None, None)
+        for r in range(1, world):
+            src, up, down = plans[r]
+            assert src is not None and 0 <= src < r
+            hops, at = 0, r
+            while at != 0:                      # following the sources reaches the root
+                at = plans[at][0]
+                hops += 1
+            assert hops == (r if world > 2 else 1)
+            if up is not None:
+                assert plans[up][2] == r        # my upstream's downstream is me
+            if down is not None:
+                assert plans[down][1] == r and plans[down][0] == r
+            assert (up is None) == (src == 0)   # the root's B needs no flags
+        star = [multi.chain_plan(world, r, "star") for r in range(world)]
+        assert all(p == (0, None, None) for p in star[1:])
