@@ -7,10 +7,10 @@
 // failed, and it also compares host kernel 0 with device kernel 0 (the reference never does).
 //
 //   cux_demo [--len N] [--quick] [--device-fill] [--pinned] [--device-only] [--gemm-block B]
-//            [--linear M N K] [--scan-len N]
+//            [--gemm-range LO HI] [--linear M N K] [--scan-len N]
 //   BASELINE sizes through the cux harness:
-//   cux_demo --device-only --device-fill --len 268435456 --gemm-block 512 --gemm-range -1 1 \\
-//            --linear 8192 8192 8192 --scan-len 1073741824
+//   cux_demo --device-only --device-fill --len 268435456 --gemm-block 512 --gemm-range -1 1
+//            --linear 8192 8192 8192 --scan-len 1073741824     (one command line)
 //   (--gemm-range -1 1: with K = 7680 the reference's [-2,5] fill makes |C| ~ 17000, which fp16 storage
 //    cannot hold exactly, so the fp16 kernel would fail cux's 1e-3 mean-error rule against the fp32 one)
 #include <cstring>
