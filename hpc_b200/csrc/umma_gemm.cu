@@ -223,6 +223,7 @@ struct UmmaArgs {
   float alpha, beta;
   int tiles_m, tiles_n;  // in units of (UG_BLOCK_M * kCtaGroup) x UG_BLOCK_N
   int k_blocks;
+  int group_m;           // tile rows per rasterisation group (L2 reuse)
   // fused B broadcast (multi-GPU, non-root ranks): column panel p of B (= n-block p) may be loaded
   // once b_ready[p] >= ready_target; the CTA's otherwise idle warp 3 pulls B from the root GPU.
   unsigned int *b_ready;
@@ -371,12 +372,12 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const int num_clusters = gridDim.x / CG;
   const int cluster_id = blockIdx.x / CG;
   const int total_tiles = p.tiles_m * p.tiles_n;
-  const int per_group = UG_GROUP_M * p.tiles_n;
+  const int per_group = p.group_m * p.tiles_n;
 
   auto tile_coord = [&](int t, int &tm, int &tn) {
     const int group = t / per_group;
-    const int first_m = group * UG_GROUP_M;
-    const int gsz = min(p.tiles_m - first_m, UG_GROUP_M);
+    const int first_m = group * p.group_m;
+    const int gsz = min(p.tiles_m - first_m, p.group_m);
     tm = first_m + (t % per_group) % gsz;
     tn = (t % per_group) / gsz;
   };
@@ -662,6 +663,7 @@ static int make_map(cuxb_ctx *ctx, CUtensorMap *map, const void *base, int ebyte
 }
 
 static int g_force_cta_group = 0;  // test hook: 0 = auto (2), 1 or 2
+static int g_group_m = UG_GROUP_M;  // test hook: rasterisation group height
 
 template <int KIND, bool B_MN, int CT, int CG>
 static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, float alpha, const void *A, int lda,
@@ -686,6 +688,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   p.tiles_m = (int)div_up(M, UG_BLOCK_M * CG);
   p.tiles_n = (int)div_up(N, UG_BLOCK_N);
   p.k_blocks = (int)div_up(K, kBlockK);
+  p.group_m = g_group_m;
   p.b_ready = nullptr, p.ready_target = 0;
   p.chain_local = nullptr, p.chain_up = nullptr, p.chain_down = nullptr, p.done_ctr = nullptr, p.done_target = 0;
   const int total = p.tiles_m * p.tiles_n;
@@ -789,6 +792,11 @@ int umma_smem_bytes() { return UmmaCfg<2>::kSmemBytes; }
 using namespace cuxb;
 
 // test hook (not in cuxb.h): force the single-CTA (1) or paired-CTA (2) MMA variant; 0 = default
+CUXB_API int cuxb_debug_set_group_m(int g) {
+  if (g < 1 || g > 64) return CUXB_ERR_INVALID;
+  g_group_m = g;
+  return 0;
+}
 CUXB_API int cuxb_debug_set_cta_group(int cg) {
   if (cg < 0 || cg > 2) return CUXB_ERR_INVALID;
   g_force_cta_group = cg;

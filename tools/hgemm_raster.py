@@ -1,0 +1,24 @@
+"""fp16 GEMM 16384^3: rasterisation group height (tile rows per group) vs sustained rate and clocks."""
+import os, sys, ctypes, subprocess
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from hpc_b200 import capi
+ctx = capi.Context(0)
+L = capi.lib()
+n = 16384
+A = torch.randint(-10, 10, (n, n), device="cuda").half()
+B = torch.randint(-10, 10, (n, n), device="cuda").half()
+C = torch.zeros(n, n, device="cuda", dtype=torch.float16)
+f = lambda: ctx.hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n, capi.FLOAT16, torch.cuda.current_stream().cuda_stream)
+for g in [int(x) for x in (sys.argv[1:] or ["8", "4", "6", "12", "16", "8"])]:
+    L.cuxb_debug_set_group_m(g)
+    for _ in range(3): f()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 60
+    e0.record()
+    for _ in range(reps): f()
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    clk = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,power.draw", "--format=csv,noheader"], capture_output=True, text=True).stdout.strip()
+    print("group_m %2d  %.3f ms  %.0f TFLOP/s   (after: %s)" % (g, ms, 2.0 * n ** 3 / ms * 1e-9, clk))
