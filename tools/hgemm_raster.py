@@ -12,10 +12,10 @@ C = torch.zeros(n, n, device="cuda", dtype=torch.float16)
 f = lambda: ctx.hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n, capi.FLOAT16, torch.cuda.current_stream().cuda_stream)
 for g in [int(x) for x in (sys.argv[1:] or ["8", "4", "6", "12", "16", "8"])]:
     L.cuxb_debug_set_group_m(g)
-    for _ in range(3): f()
+    for _ in range(int(os.environ.get('WARM', '3'))): f()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    reps = 60
+    reps = int(os.environ.get('REPS', '60'))
     e0.record()
     for _ in range(reps): f()
     e1.record(); torch.cuda.synchronize()
