@@ -37,6 +37,7 @@ N_SCAN = 1 << 30
 SGEMM_N = 8192
 HGEMM_N = 16384
 LIN8_N = 8192
+SHARE = 1   # --scaling strong: every size above is the WHOLE job and each of the N GPUs takes 1/N of it
 FP32_FFMA_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.4: 148 SMs x 128 lanes x 2 x clocks.max.sm
 INT8_NOMINAL_TOPS = 4500.0
 
@@ -120,7 +121,7 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
     stream = lambda: torch.cuda.current_stream().cuda_stream
     seed = 20240607 + 17 * rank
     if name in ("dot", "sum", "nrm2"):
-        n = N_DOT
+        n = N_DOT // SHARE
         a = W.gen_int((n,), -2, 2, torch.float32, seed)        # cux fill, demo.cpp:30
         b = W.gen_int((n,), -2, 2, torch.float32, seed + 1) if name == "dot" else None
         res = torch.zeros(1, device="cuda")
@@ -166,7 +167,7 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
                     "combine": None if name == "nrm2" else "sum", "keep": (ha, hb)}
         W.make_e2e = make_e2e
     elif name == "scan":
-        n = N_SCAN
+        n = N_SCAN // SHARE
         x = W.gen_int((n,), -2, 2, torch.int32, seed)
         out = torch.empty_like(x)
         tot = torch.zeros(1, dtype=torch.int32, device="cuda")
@@ -205,29 +206,32 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
     elif name in ("sgemm", "hgemm", "linear_s8"):
         if name == "sgemm":
             n = SGEMM_N
-            A = W.gen_int((n, n), -2, 5, torch.float32, seed)
+            m = n // SHARE
+            A = W.gen_int((m, n), -2, 5, torch.float32, seed)
             B = W.gen_int((n, n), -2, 5, torch.float32, 20240607 + 99)   # B identical on every rank
-            C = torch.zeros((n, n), device="cuda")
-            fn = lambda: ctx.sgemm_f32(n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n, stream())
+            C = torch.zeros((m, n), device="cuda")
+            fn = lambda: ctx.sgemm_f32(m, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n, stream())
             W.dtype, W.peak_kind = "f32", "ffma"
             W.desc = "fp32 SGEMM %d^3 per GPU on CUDA cores (configs[2]); rows of C sharded, B replicated" % n
             W.metric = "GEMM TFLOP/s (fp32 SGEMM 8192^3 per GPU, CUDA cores)"
         elif name == "hgemm":
             n = HGEMM_N
-            A = W.gen_int((n, n), -10, 9, torch.float16, seed)
+            m = n // SHARE
+            A = W.gen_int((m, n), -10, 9, torch.float16, seed)
             B = W.gen_int((n, n), -10, 9, torch.float16, 20240607 + 99)
-            C = torch.zeros((n, n), dtype=torch.float16, device="cuda")
-            fn = lambda: ctx.hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n,
+            C = torch.zeros((m, n), dtype=torch.float16, device="cuda")
+            fn = lambda: ctx.hgemm_f16(m, n, n, 1.0, A.data_ptr(), n, B.data_ptr(), n, 0.0, C.data_ptr(), n,
                                        capi.FLOAT16, stream())
             W.dtype, W.peak_kind = "f16 (fp32 accumulate)", "tensor"
             W.desc = "fp16 GEMM %d^3 per GPU, fp32 accumulate, tcgen05/TMEM (configs[3]); rows of C sharded, B replicated" % n
             W.metric = "GEMM TFLOP/s (fp16 GEMM 16384^3 per GPU, fp32 accumulate, tcgen05)"
         else:
             n = LIN8_N
-            A = W.gen_int((n, n), 0, 16, torch.int8, seed)
+            m = n // SHARE
+            A = W.gen_int((m, n), 0, 16, torch.int8, seed)
             B = W.gen_int((n, n), -8, 8, torch.int8, 20240607 + 99)
-            C = torch.zeros((n, n), dtype=torch.int32, device="cuda")
-            fn = lambda: ctx.linear_s8(n, n, n, A.data_ptr(), B.data_ptr(), C.data_ptr(), stream())
+            C = torch.zeros((m, n), dtype=torch.int32, device="cuda")
+            fn = lambda: ctx.linear_s8(m, n, n, A.data_ptr(), B.data_ptr(), C.data_ptr(), stream())
             W.dtype, W.peak_kind = "s8 (int32 accumulate)", "tensor_int8"
             W.desc = "int8 linear %d^3 per GPU, int32 accumulate, tcgen05 kind::i8 (configs[4])" % n
             W.metric = "GEMM TOP/s (int8 linear 8192^3 per GPU, int32 accumulate)"
@@ -247,15 +251,15 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
             is_root = rank == 0
             W.step_nccl = fn  # comparison: B already resident on every GPU (no broadcast in the step)
             if name == "hgemm":
-                W.step = lambda: ctx.mg_hgemm_f16(n, n, n, 1.0, A.data_ptr(), n, b_up, bsym.ptrs[rank], n, 0.0,
+                W.step = lambda: ctx.mg_hgemm_f16(m, n, n, 1.0, A.data_ptr(), n, b_up, bsym.ptrs[rank], n, 0.0,
                                                   C.data_ptr(), n, is_root, capi.FLOAT16, stream())
                 how = "by the otherwise idle warp of every CTA (TMA), column panel by column panel"
             elif name == "sgemm":
-                W.step = lambda: ctx.mg_sgemm_f32(n, n, n, 1.0, A.data_ptr(), n, b_up, bsym.ptrs[rank], n, 0.0,
+                W.step = lambda: ctx.mg_sgemm_f32(m, n, n, 1.0, A.data_ptr(), n, b_up, bsym.ptrs[rank], n, 0.0,
                                                   C.data_ptr(), n, is_root, stream())
                 how = "by the first 48 CTAs of the launch (the slots its last wave of tiles leaves idle), 128 rows of B per readiness flag"
             else:
-                W.step = lambda: ctx.mg_linear_s8(n, n, n, A.data_ptr(), b_up, bsym.ptrs[rank], C.data_ptr(),
+                W.step = lambda: ctx.mg_linear_s8(m, n, n, A.data_ptr(), b_up, bsym.ptrs[rank], C.data_ptr(),
                                                   is_root, stream())
                 how = "by the otherwise idle warp of every CTA (TMA), n-block panel by n-block panel"
             route = ("from the rank before it (chain: each GPU sends B once)" if bcast == "chain"
@@ -270,17 +274,17 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
             hA, hB = pin(A), pin(B)
             hC = torch.empty(C.shape, dtype=C.dtype, pin_memory=True)
             if name == "sgemm":
-                call = lambda: ctx.sgemm_f32_host(n, n, n, 1.0, hA.data_ptr(), n, hB.data_ptr(), n, 0.0, hC.data_ptr(), n)
+                call = lambda: ctx.sgemm_f32_host(m, n, n, 1.0, hA.data_ptr(), n, hB.data_ptr(), n, 0.0, hC.data_ptr(), n)
             elif name == "hgemm":
-                call = lambda: ctx.hgemm_f16_host(n, n, n, 1.0, hA.data_ptr(), n, hB.data_ptr(), n, 0.0, hC.data_ptr(), n,
+                call = lambda: ctx.hgemm_f16_host(m, n, n, 1.0, hA.data_ptr(), n, hB.data_ptr(), n, 0.0, hC.data_ptr(), n,
                                                   capi.FLOAT16)
             else:
-                call = lambda: ctx.linear_s8_host(n, n, n, hA.data_ptr(), hB.data_ptr(), hC.data_ptr())
+                call = lambda: ctx.linear_s8_host(m, n, n, hA.data_ptr(), hB.data_ptr(), hC.data_ptr())
             api = {"sgemm": "cuxb_sgemm_f32_host", "hgemm": "cuxb_hgemm_f16_f32acc_host", "linear_s8": "cuxb_linear_s8_s32_host"}[name]
             return {"call": call, "h2d": (A.numel() + B.numel()) * A.element_size(), "d2h": C.numel() * C.element_size(),
                     "api": api, "result": hC[-1, -1:], "combine": None, "keep": (hA, hB, hC)}
         W.make_e2e = make_e2e
-        W.units = 2 * n * n * n
+        W.units = 2 * m * n * n
         W.unit = "TOP/s" if name == "linear_s8" else "TFLOP/s"
         W.bound = "tensor" if name != "sgemm" else "ffma"
         W.result = C[-1, -1:]
@@ -485,6 +489,9 @@ def main():
                     help="N>1: exchange fused into the kernel over peer memory (default) or a NCCL collective after it")
     ap.add_argument("--bcast", default="chain", choices=["chain", "star"],
                     help="N>1 GEMMs: pull B from the previous rank's copy (default) or every rank from the root")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: the named size PER GPU (default, what the driver's 1-8 GPU run uses); strong: the named size is "
+                         "the whole job, each GPU takes 1/N of the elements (vectors) or of the rows of A and C (GEMMs)")
     ap.add_argument("--no-also", action="store_true", help="skip the short passes over the other workloads")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     args = ap.parse_args()
@@ -498,6 +505,9 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.scaling == "strong":
+        global SHARE
+        SHARE = world
     torch.cuda.set_device(local)
     dist = None
     if world > 1:
@@ -623,13 +633,18 @@ def main():
 
     if rank == 0:
         wl = make_desc(args.workload)
+        if args.scaling == "strong" and world > 1:   # the named size is the whole job
+            for k in ("metric", "desc"):
+                wl[k] = wl[k].replace(" per GPU", " in total, 1/%d of it per GPU" % world)
         line = {
             "metric": wl["metric"], "value": value, "unit": wl["unit"], "n_gpus": world, "steps": args.steps,
-            "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": wl["dtype"], "data": "synthetic",
             "config": {"workload": wl["desc"], "l2": "inputs larger than L2 (no flush needed)" if wl["hbm"] else
-                       "GEMM operands exceed L2; no flush", "parallelism": "one rank per GPU, per-GPU partial + one NCCL all-reduce"
-                       if wl["hbm"] else "rows of C sharded per GPU, B replicated"},
+                       "GEMM operands exceed L2; no flush",
+                       "parallelism": "1 GPU" if world == 1 else
+                       ("one rank per GPU, contiguous slice each; " if wl["hbm"] else "one rank per GPU, rows of A and C sharded; ")
+                       + collective_desc},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "collective": collective_desc, "nccl_variant": nccl_variant, "also": also,
         }
