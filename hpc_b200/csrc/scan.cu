@@ -392,8 +392,7 @@ static int launch_scan(int device, cudaStream_t st, unsigned int grid, const T *
       smem_set.fetch_or(bit, std::memory_order_release);
     }
   }
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
+  cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid, 1, 1);
   cfg.blockDim = dim3(kScanCtaThreads, 1, 1);
   cfg.dynamicSmemBytes = kScanSmemBytes;

@@ -742,8 +742,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
       smem_set.fetch_or(bit, std::memory_order_release);
     }
   }
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
+  cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(clusters * CG, 1, 1);
   cfg.blockDim = dim3(UG_THREADS, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
