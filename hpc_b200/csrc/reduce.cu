@@ -185,10 +185,23 @@ reduce_kernel(const T *__restrict__ a, const T *__restrict__ b, long long n,
       acc2 += fold4<OP, T>(x2, y2);
       acc3 += fold4<OP, T>(x3, y3);
     }
-    for (; i < nvec; i += stride) {
-      V x0 = ldg_stream(a4 + i), y0 = x0;
-      if (OP == OP_DOT) y0 = ldg_stream(b4 + i);
-      acc0 += fold4<OP, T>(x0, y0);
+    // at most three vectors per thread are left: issue their loads together, then fold (a loop
+    // would wait for each load in turn -- most of a short vector's run time)
+    {
+      const bool p0 = i < nvec, p1 = i + stride < nvec, p2 = i + 2 * stride < nvec;
+      V x0 = {}, x1 = {}, x2 = {};
+      if (p0) x0 = ldg_stream(a4 + i);
+      if (p1) x1 = ldg_stream(a4 + i + stride);
+      if (p2) x2 = ldg_stream(a4 + i + 2 * stride);
+      V y0 = x0, y1 = x1, y2 = x2;
+      if (OP == OP_DOT) {
+        if (p0) y0 = ldg_stream(b4 + i);
+        if (p1) y1 = ldg_stream(b4 + i + stride);
+        if (p2) y2 = ldg_stream(b4 + i + 2 * stride);
+      }
+      if (p0) acc0 += fold4<OP, T>(x0, y0);
+      if (p1) acc0 += fold4<OP, T>(x1, y1);
+      if (p2) acc0 += fold4<OP, T>(x2, y2);
     }
     // n % 4 trailing scalars: one per thread of CTA 0
     const long long rem = (nvec << 2) + tid;

@@ -337,7 +337,7 @@ Gemm::Gemm(OpAssistor *assistor, GemmKernelParam &params) : Operator(assistor), 
   {  // device V0: fp32 on CUDA cores
     auto *k = new GemmGpuKernelIF();
     k->type_flag = TypeFlag::FLOAT32;
-    k->describe_info = "cuxb sm_100a SGEMM: 128x128x16 CTA tile, 8x8 FFMA micro-tile, double-buffered shared memory";
+    k->describe_info = "cuxb sm_100a SGEMM: 128x128x16 CTA tile, 8x8 micro-tile on packed FFMA2, double-buffered shared memory, deterministic split-K for small problems";
     k->get_config = [tile_config](int M, int N) { return tile_config(M, N, 128, 128, 256); };
     k->func = [as](Config2D, const int M, const int N, const int K, const float alpha, const void *A, const int lda,
                    const void *B, const int ldb, const float beta, void *C, const int ldc) {
