@@ -247,7 +247,7 @@ struct UmmaCfg {
   static constexpr int kBBytes = kBRows * UG_ROW_BYTES;             // 16 / 32 KiB
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (CG == 2) ? 6 : 4;
-  static constexpr int kCopyBufBytes = 12288;  // one 256-column x 24-row box of 16-bit B (broadcast staging)
+  static constexpr int kCopyBufBytes = 16384;  // one 256 x 32 box of 16-bit B or 256 x 64 of int8 (broadcast staging)
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 1024 /*barriers*/ + 2 * kCopyBufBytes;
 };
 
@@ -458,12 +458,12 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // ===================== broadcast warp (multi-GPU, non-root ranks only) =====================
     // Pulls B from the root GPU's memory over NVLink into the local copy, panel by panel in the
     // order the tiles consume them (panel = the 256 output columns of one n-block): TMA load (peer
-    // global -> shared), TMA store (shared -> local global), two boxes in flight.  B[K,N] (B_MN): a
-    // panel is 256 columns x K rows, boxes of 256 columns x 24 rows.  Bt[N,K] (K-major): a panel is
+    // global -> shared), TMA store (shared -> local global), two 16 KiB boxes in flight.  B[K,N] (B_MN): a
+    // panel is 256 columns x K rows, boxes of 256 columns x 32 rows.  Bt[N,K] (K-major): a panel is
     // 256 rows x K columns, boxes of 256 k x kPullRows rows.  Box c of a panel belongs to CTA
     // (c mod grid).  When this CTA's share of a panel has landed it bumps the panel's counter (release).
     if (p.b_ready != nullptr && elect_one()) {
-      constexpr int kPullRows = B_MN ? 24 : (KIND == KIND_S8 ? 32 : 16);
+      constexpr int kPullRows = (KIND == KIND_S8) ? 64 : 32;
       constexpr uint32_t kPullBytes = 256u * kPullRows * (KIND == KIND_S8 ? 1 : 2);
       static_assert(kPullBytes <= (uint32_t)Cfg::kCopyBufBytes, "broadcast staging buffer too small");
       constexpr int kRowBoxes = UG_BLOCK_N / kPullRows;          // K-major only: row chunks per panel
@@ -698,9 +698,9 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   CUtensorMap msrc = mb, mdst = mb;  // unused unless B is pulled from another GPU
   if (b_pull_from != nullptr) {
     CUXB_REQUIRE(p.tiles_n <= 4096, CUXB_ERR_TOO_LARGE, "fused B broadcast: N too large");
-    // un-swizzled copy boxes (see the broadcast warp): 256 elements wide, 24 / 32 / 16 rows
+    // un-swizzled copy boxes (see the broadcast warp): 256 elements wide, 32 rows (64 for int8) = 16 KiB
     const uint64_t rows = B_MN ? (uint64_t)K : (uint64_t)N, cols = B_MN ? (uint64_t)N : (uint64_t)K;
-    const uint32_t box_rows = B_MN ? 24 : (KIND == KIND_S8 ? 32 : 16);
+    const uint32_t box_rows = (KIND == KIND_S8) ? 64 : 32;
     rc = make_map(ctx, &msrc, b_pull_from, ebytes, dt, rows, cols, (uint64_t)ldb, 256, box_rows, false);
     if (rc) return rc;
     rc = make_map(ctx, &mdst, B, ebytes, dt, rows, cols, (uint64_t)ldb, 256, box_rows, false);

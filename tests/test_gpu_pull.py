@@ -212,7 +212,7 @@ def test_chained_broadcast_flag_protocol_sequential():
 
 @pytest.mark.parametrize("kind", ["bf16", "f16"])
 def test_linear_16bit_pull_bit_exact(kind):
-    """K-major 16-bit Bt pulled in 256-k x 16-row boxes; integer fills, so bit-exact vs the plain kernel and,
+    """K-major 16-bit Bt pulled in 256-k x 32-row boxes; integer fills, so bit-exact vs the plain kernel and,
     for bf16, vs LinearNormalBf16 (linear.cpp:137-151)."""
     M, N, K = 384, 1096, 1096   # ragged N and K (multiples of 8 only: 16-byte row pitches)
     A = dg.int_fill((M, K), -4, 4, tag=51)
