@@ -904,7 +904,7 @@ CUXB_API int cuxb_mg_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, in
                                                     pull);
 }
 
-// The same for the 16-bit linears (linear.cpp:137-182's layout): Bt[N,K] pulled in 256-k x 16-row boxes.
+// The same for the 16-bit linears (linear.cpp:137-182's layout): Bt[N,K] pulled in 256-k x 32-row boxes.
 CUXB_API int cuxb_mg_linear_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A,
                                         const void *bt_root, void *bt_local, void *C, int c_dtype, int is_root) {
   CUXB_REQUIRE(c_dtype == CUXB_BFLOAT16 || c_dtype == CUXB_FLOAT32, CUXB_ERR_INVALID,
