@@ -77,6 +77,7 @@ struct cuxb_ctx {
   unsigned int *bcast_ready;   // fused B broadcast: per-panel arrival counters (grow by grid size per call)
   unsigned int bcast_calls;
   int bcast_grid, bcast_panels;
+  unsigned int *wave_sync;         // tcgen05 GEMM: per-launch arrival counter of the soft wave rendezvous
   unsigned int bcast_done_total;   // chained broadcast: panels published so far (all calls)
   unsigned int *chain_local;       // chained broadcast flags (cuxb_mg_set_chain), peer-mapped
   const unsigned int *chain_up, *chain_down;

@@ -95,6 +95,7 @@ CUXB_API int cuxb_ctx_destroy(cuxb_ctx *c) {
   if (c->red_ticket) cudaFree(c->red_ticket);
   if (c->scan_state) cudaFree(c->scan_state);
   if (c->bcast_ready) cudaFree(c->bcast_ready);
+  if (c->wave_sync) cudaFree(c->wave_sync);
   if (c->sg_scratch) cudaFree(c->sg_scratch);
   if (c->sg_pull) cudaFree(c->sg_pull);
   for (int i = 0; i < 4; i++)
