@@ -288,3 +288,17 @@ CUXB_API int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *activ
   if (dynamic_smem_bytes) *dynamic_smem_bytes = smem;
   return 0;
 }
+
+// test hook (not in cuxb.h): rows per chunk the host pipelines would use; kind 0 = fp32 sgemm, 1 = fp16
+// gemm (fp16 out), 2 = int8 linear.  Pure host arithmetic, callable without a GPU.
+CUXB_API int cuxb_debug_host_chunk_rows(int kind, int M, int N, int K, int sm_count) {
+  PipeCost c;
+  const int ab = kind == 0 ? 4 : (kind == 1 ? 2 : 1), cb = kind == 1 ? 2 : 4;
+  const int gran = kind == 0 ? 128 : 256, slots = kind == 0 ? 2 * sm_count : sm_count / 2;
+  const double rate = kind == 0 ? 60e12 : (kind == 1 ? 1.6e15 : 3.2e15);
+  c.up_b_bytes = (double)K * N * ab;
+  c.up_row_bytes = (double)K * ab;
+  c.down_row_bytes = (double)N * cb;
+  c.wave_seconds = 2.0 * gran * gran * (double)K * slots / rate;
+  return pipe_chunk_rows(M, gran, (N + gran - 1) / gran, slots, c);
+}

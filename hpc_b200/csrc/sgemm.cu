@@ -382,6 +382,38 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   }
 }
 
+// Split count for a problem of `tiles` output tiles and depth K on a GPU with room for `room` CTAs.
+// Pure host arithmetic (tests/test_abi.py exercises it without a GPU through cuxb_debug_sgemm_splits).
+// Pick the split count whose last wave is fullest (efficiency = work / (waves * room)); splitting costs
+// one round trip of the accumulators through L2, so it has to buy at least 8 %.  At least 64 k per
+// split, at most 32 splits and 1024 CTAs; then rounded so that every split is a whole number of k-tiles.
+int sgemm_pick_splits(int tiles, int K, int room) {
+  int splits = 1;
+  if (tiles <= 1024 && K >= 256) {
+    auto eff = [&](int sp) {
+      const int ctas = tiles * sp;
+      const int waves = (ctas + room - 1) / room;
+      return (double)ctas / ((double)waves * room);
+    };
+    double best = eff(1) * 1.08;
+    const int max_sp = K / 64 < 32 ? K / 64 : 32;
+    for (int sp = 2; sp <= max_sp && tiles * sp <= 1024; sp++)
+      if (eff(sp) > best) best = eff(sp), splits = sp;
+  }
+  if (splits > 1) {
+    int kps = (K + splits - 1) / splits;
+    kps = (kps + SG_BK - 1) / SG_BK * SG_BK;
+    splits = (K + kps - 1) / kps;
+  }
+  return splits;
+}
+
+// Copy CTAs of the fused-broadcast launch: the slots the last wave of tiles leaves idle (16..63), else 64.
+int sgemm_pick_copy_ctas(int tiles, int room) {
+  const int spare = (tiles % room) ? room - tiles % room : 0;
+  return (spare >= 16 && spare < 64) ? spare : 64;
+}
+
 const void *sgemm_kernel_symbol() { return (const void *)sgemm_kernel<true, false>; }
 
 }  // namespace cuxb
@@ -414,25 +446,7 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
   p.Bsrc = nullptr, p.pull_ready = nullptr, p.pull_ticket = nullptr, p.ticket_base = 0, p.ready_target = 0, p.panels = 0, p.n_copy = 0;
   p.chain_local = nullptr, p.chain_up = nullptr, p.chain_down = nullptr, p.done_ctr = nullptr, p.done_target = 0;
   const int room = 2 * ctx->sm_count;  // CTAs resident at once
-  int splits = 1;
-  if (tiles <= 1024 && K >= 256) {
-    // pick the split count whose last wave is fullest (efficiency = work / (waves * room)); splitting
-    // costs one round trip of the accumulators through L2, so it has to buy at least 8 %
-    auto eff = [&](int sp) {
-      const int ctas = tiles * sp;
-      const int waves = (ctas + room - 1) / room;
-      return (double)ctas / ((double)waves * room);
-    };
-    double best = eff(1) * 1.08;
-    const int max_sp = K / 64 < 32 ? K / 64 : 32;  // at least 64 k per split
-    for (int sp = 2; sp <= max_sp && tiles * sp <= 1024; sp++)
-      if (eff(sp) > best) best = eff(sp), splits = sp;
-  }
-  if (splits > 1) {
-    int kps = (K + splits - 1) / splits;
-    kps = (kps + SG_BK - 1) / SG_BK * SG_BK;
-    splits = (K + kps - 1) / kps;
-  }
+  const int splits = sgemm_pick_splits(tiles, K, room);
   if (splits > 1) {
     // layout: [0, 4096) per-tile tickets (tiles <= 1024; zero at rest), then the parked accumulators
     const size_t need = 4096 + (size_t)tiles * splits * 16 * SG_THREADS * sizeof(float4);
@@ -505,8 +519,7 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
   }
   const int tiles = p.tiles_m * p.tiles_n;
   const int room = 2 * ctx->sm_count;
-  const int spare = (tiles % room) ? room - tiles % room : 0;
-  p.n_copy = (spare >= 16 && spare < 64) ? spare : 64;
+  p.n_copy = sgemm_pick_copy_ctas(tiles, room);
   // the flags only grow, by n_copy per call for each of the call's panels: a different panel count or
   // n_copy would leave them uneven, so start over from zero when either changes (ordered on the stream)
   if (ctx->sg_pull_panels != p.panels || ctx->sg_pull_ncopy != p.n_copy) {
@@ -532,4 +545,13 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
   sgemm_kernel<true, false, true><<<grid, SG_THREADS, 0, st>>>(p);
   CUXB_LAUNCHED();
   return 0;
+}
+
+// test hooks (not in cuxb.h): the host-side planning arithmetic, callable without a GPU
+CUXB_API int cuxb_debug_sgemm_splits(int M, int N, int K, int sm_count) {
+  const int tiles = ((M + SG_BM - 1) / SG_BM) * ((N + SG_BN - 1) / SG_BN);
+  return sgemm_pick_splits(tiles, K, 2 * sm_count);
+}
+CUXB_API int cuxb_debug_sgemm_copy_ctas(int M, int N, int sm_count) {
+  return sgemm_pick_copy_ctas((M / SG_BM) * (N / SG_BN), 2 * sm_count);
 }

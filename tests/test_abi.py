@@ -66,3 +66,33 @@ def test_product_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "import oracle" not in text and "from oracle" not in text, f
                 assert "liboracle" not in text and "libcuxref" not in text, f
+
+
+def test_host_side_planning_arithmetic_without_a_gpu():
+    """The launch planning that is pure host arithmetic, through the library's test hooks: split-K count of the
+    SGEMM (sgemm.cu), copy-CTA count of its fused broadcast, chunk size of the host-buffer pipelines
+    (host_api.cu).  B200 = 148 SMs -> 296 SGEMM CTA slots, 74 tcgen05 cluster slots."""
+    L = capi.lib()
+    sm = 148
+    # big problems are never split; the reference's split-K case and cux's demo shape are
+    assert L.cuxb_debug_sgemm_splits(8192, 8192, 8192, sm) == 1
+    assert L.cuxb_debug_sgemm_splits(1280, 2048, 4096, sm) > 1      # 160 tiles on 296 slots
+    s = L.cuxb_debug_sgemm_splits(64, 64, 4096, sm)                   # one tile, K = 4096
+    assert 16 <= s <= 32
+    assert L.cuxb_debug_sgemm_splits(512, 576, 480, sm) in range(2, 8)
+    assert L.cuxb_debug_sgemm_splits(128, 128, 128, sm) == 1          # K < 256: not worth a round trip
+    for (M, N, K) in [(64, 64, 4096), (512, 576, 480), (256, 256, 1000), (1280, 2048, 4096)]:
+        sp = L.cuxb_debug_sgemm_splits(M, N, K, sm)
+        tiles = -(-M // 128) * -(-N // 128)
+        assert tiles * sp <= 1024 and (sp == 1 or -(-K // sp) >= 64)
+    # fused broadcast: the copy CTAs fit into what the last wave of tiles leaves idle
+    assert L.cuxb_debug_sgemm_copy_ctas(8192, 8192, sm) == 48          # 4096 tiles = 13 x 296 + 248
+    assert L.cuxb_debug_sgemm_copy_ctas(128 * 296, 128, sm) == 64      # no slack at all
+    assert L.cuxb_debug_sgemm_copy_ctas(128 * 290, 128, sm) == 64      # 6 idle slots are too few to copy with
+    # host pipelines: small problems are one chunk; big ones a multiple of the tile height, at most 16 chunks
+    assert L.cuxb_debug_host_chunk_rows(0, 256, 384, 128, sm) == 256
+    for kind, (M, N, K), gran in [(0, (8192, 8192, 8192), 128), (1, (16384, 16384, 16384), 256),
+                                  (2, (8192, 8192, 8192), 256), (0, (4224, 1024, 1024), 128)]:
+        per = L.cuxb_debug_host_chunk_rows(kind, M, N, K, sm)
+        assert 0 < per <= M and (per % gran == 0 or per == M)
+        assert 2 <= -(-M // per) <= 16
