@@ -550,6 +550,16 @@ def main():
     # ---- the dominant kernel alone, on the launching stream (roofline.achieved)
     ms_k, _, t1k = time_steps(torch, W.kernel, args.steps, 3, None)
     ms_kernel = ms_k / args.steps
+    # spread of single launches (cux's GpuTimer protocol, timer.h:16-38: one event pair per run), reported
+    # next to the average the roofline uses
+    n_single = max(5, min(args.steps, 50))
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_single)]
+    for a_, b_ in evs:
+        a_.record()
+        W.kernel()
+        b_.record()
+    torch.cuda.synchronize()
+    singles = sorted(a_.elapsed_time(b_) for a_, b_ in evs)
     clocks = None
     if rank == 0:
         # nvidia-smi cannot sample faster than ~10 Hz: keep the GPU under the same load a little longer
@@ -563,7 +573,9 @@ def main():
     peak, punit, pnote = peak_for(W, peaks)
     roofline = {"bound": "hbm" if W.bound == "hbm" else "tensor" if W.bound == "tensor" else "ffma",
                 "achieved": achieved, "peak": peak, "unit": punit, "frac": achieved / peak,
-                "traffic": None, "kernel_ms": ms_kernel, "peak_source": pnote,
+                "traffic": None, "kernel_ms": ms_kernel, "kernel_ms_median": singles[len(singles) // 2],
+                "kernel_ms_min": singles[0], "kernel_ms_max": singles[-1], "single_launches_timed": n_single,
+                "peak_source": pnote,
                 "algorithmic_units_per_launch": W.units}
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
