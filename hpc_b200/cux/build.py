@@ -3,6 +3,7 @@
     hpc_b200/cux/libcux_host.so   the framework (Executor, ops, Array4D, ...)
     hpc_b200/cux/cux_demo         example/demo.cpp + example/user_plugins.cpp
     hpc_b200/cux/cux_host_test    tests/host_test.cpp (runs without a GPU)
+    hpc_b200/cux/cux_device_test  tests/device_test.cpp (the reference's DataTest cases; needs a B200)
 All link against hpc_b200/libcuxb.so through include/cuxb.h only.
 """
 import os
@@ -50,6 +51,10 @@ def build(force=False):
     tsrc = [os.path.join(HERE, "tests", "host_test.cpp")]
     if force or _stale(test, tsrc + hdrs + [lib]):
         run(CXX + INC + ["-o", test] + tsrc + ["-L" + HERE, "-lcux_host"] + LINK)
+    dtest = os.path.join(HERE, "cux_device_test")
+    dtsrc = [os.path.join(HERE, "tests", "device_test.cpp")]
+    if force or _stale(dtest, dtsrc + hdrs + [lib]):
+        run(CXX + INC + ["-o", dtest] + dtsrc + ["-L" + HERE, "-lcux_host"] + LINK)
     return lib, demo, test
 
 

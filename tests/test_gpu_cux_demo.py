@@ -43,3 +43,14 @@ def test_demo_with_device_side_fill_and_pinned_host_memory():
     r = run_demo("--quick", "--device-fill", "--pinned")
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "cux_demo: all checks passed" in r.stdout and "Fail" not in r.stdout
+
+
+def test_reference_data_test_cases_on_the_device():
+    """hpc_b200/cux/tests/device_test.cpp: the reference's own DataTest suite (tests/data_test.cpp:104-143 --
+    push and back for int32 / float / half / int8, conversions, Save / Restore) against this Array4D, with
+    pageable and pinned host copies, plus the device-side extensions."""
+    exe = os.path.join(ROOT, "hpc_b200", "cux", "cux_device_test")
+    assert os.path.exists(exe), "run __graft_entry__.build() first"
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=200)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "cux_device_test: all passed" in r.stdout and "FAILED" not in r.stdout
