@@ -577,6 +577,20 @@ def main():
                 "kernel_ms_min": singles[0], "kernel_ms_max": singles[-1], "single_launches_timed": n_single,
                 "peak_source": pnote,
                 "algorithmic_units_per_launch": W.units}
+    # the same ceilings measured here, by the library's own probes (N = 1 only: they take a second)
+    if world == 1 and not args.no_cpu:
+        try:
+            if W.bound == "hbm":
+                kind = "copy" if W.name == "scan" else "read"
+                roofline["measured_here"] = {"value": ctx.probe_hbm(kind, 2 << 30, 5), "unit": "GB/s",
+                                             "what": "cuxb_probe_hbm %s stream over 2 GiB, best of 5" % kind}
+            elif W.name == "sgemm":
+                roofline["measured_here"] = {"value": ctx.probe_fp32(True, 5), "unit": "TFLOP/s",
+                                             "what": "cuxb_probe_fp32: packed FFMA2 chains, best of 5"}
+            if "measured_here" in roofline:
+                roofline["measured_here"]["frac"] = achieved / roofline["measured_here"]["value"]
+        except Exception as ex:
+            roofline["measured_here"] = {"error": str(ex)[:200]}
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         roofline["traffic"] = json.load(open(tpath)).get(W.name)

@@ -87,6 +87,8 @@ SIGNATURES = {
     "cuxb_sgemm_f32_host": ([_vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc_host": ([_vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
     "cuxb_linear_s8_s32_host": ([_vp, _i, _i, _i, _vp, _vp, _vp], _i),
+    "cuxb_probe_hbm": ([_vp, _i, C.c_size_t, _i, C.POINTER(C.c_double)], _i),
+    "cuxb_probe_fp32": ([_vp, _i, _i, C.POINTER(C.c_double)], _i),
     "cuxb_kernel_occupancy": ([_vp, C.c_char_p, C.POINTER(_i), C.POINTER(C.c_double), C.POINTER(_i),
                                C.POINTER(_i)], _i),
 }
@@ -233,6 +235,19 @@ class Context:
 
     def fill_random(self, n, dst, dtype, lo, hi, decimal_pose=0, seed=20240607, stream=0):
         check(lib().cuxb_fill_random(self._h, stream, n, dst, dtype, lo, hi, decimal_pose, seed), "cuxb_fill_random")
+
+    def probe_hbm(self, which, nbytes=2 << 30, reps=5):
+        """Measured HBM ceiling in GB/s: which = "read" | "write" | "copy"."""
+        v = C.c_double()
+        check(lib().cuxb_probe_hbm(self._h, {"read": 0, "write": 1, "copy": 2}[which], nbytes, reps, C.byref(v)),
+              "cuxb_probe_hbm")
+        return v.value
+
+    def probe_fp32(self, packed=True, reps=5):
+        """Measured FP32 rate of the CUDA cores in TFLOP/s (scalar FFMA or packed FFMA2)."""
+        v = C.c_double()
+        check(lib().cuxb_probe_fp32(self._h, int(packed), reps, C.byref(v)), "cuxb_probe_fp32")
+        return v.value
 
     def occupancy(self, kernel):
         ab, occ, th, sm = _i(), C.c_double(), _i(), _i()

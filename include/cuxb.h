@@ -292,6 +292,15 @@ int cuxb_linear_s8_s32_host(cuxb_ctx *ctx, int M, int N, int K, const int8_t *A,
 int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *active_blocks_per_sm,
                           double *occupancy, int *threads_per_block, int *dynamic_smem_bytes);
 
+/* ---- measured ceilings of this GPU, for a harness that prints roofline fractions: the counterpart of the
+ * reference's evaluation helpers (pocket-ai/eval/cuda/bandwidth_eval.hpp:257-300, timed device-to-device
+ * copies; pocket-ai/eval/cuda/max_flops.cuh:11-94, timed fma chains).  Both calls allocate their own
+ * buffers, run on the context's private stream, block until done and return the best of `reps` launches.
+ * cuxb_probe_hbm: which = 0 read-only, 1 write-only, 2 copy (a copy of `bytes` counts as 2 x bytes moved);
+ * use several times the 126 MB L2.  cuxb_probe_fp32: packed = 0 scalar FFMA, 1 packed FFMA2. */
+int cuxb_probe_hbm(cuxb_ctx *ctx, int which, size_t bytes, int reps, double *gb_per_s);
+int cuxb_probe_fp32(cuxb_ctx *ctx, int packed, int reps, double *tflops);
+
 #ifdef __cplusplus
 }
 #endif

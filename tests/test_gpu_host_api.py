@@ -181,3 +181,15 @@ def test_host_pipelines_cut_into_chunks_match_the_device_kernels():
     c.scan_i32_host(n, p(x), p(out), -5)
     want = oracle.scan_i32(x, -5)
     assert want.min() < 0 and np.array_equal(out, want)
+
+
+def test_probes_report_plausible_ceilings():
+    """cuxb_probe_hbm / cuxb_probe_fp32 (pocket-ai/eval/cuda/bandwidth_eval.hpp:257-300, max_flops.cuh:11-94 on a
+    B200): sanity ranges only -- the numbers themselves go into bench.py's roofline.measured_here."""
+    c = ctx()
+    rd, wr, cp = c.probe_hbm("read", 1 << 30, 3), c.probe_hbm("write", 1 << 30, 3), c.probe_hbm("copy", 1 << 30, 3)
+    assert 4000 < rd < 8200 and 4000 < wr < 8200 and 4000 < cp < 8200, (rd, wr, cp)
+    f1, f2 = c.probe_fp32(False, 3), c.probe_fp32(True, 3)
+    assert 40 < f1 < 80 and 40 < f2 < 80 and f2 >= 0.95 * f1, (f1, f2)
+    with pytest.raises(capi.CuxbError):
+        c.probe_hbm("read", 1000, 3)          # too small / not a multiple of 16
