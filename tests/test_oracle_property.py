@@ -65,3 +65,22 @@ def test_scan_f32_random_lengths(n, seed):
     want = np.empty(n, np.float32)
     ref.ref_scan_f32(0, x, n, want)                      # VectorScanNormal
     assert np.array_equal(bits(oracle.scan_f32(x)), bits(want))
+
+
+@settings(**CFG)
+@given(st.integers(1, 24), st.integers(1, 24), st.integers(1, 120), st.integers(0, 2 ** 31 - 1))
+def test_hgemm_and_bf16_linear_random_shapes(M, N, K, seed):
+    rng = np.random.default_rng(seed)
+    A, B = _f32(rng, (M, K)), _f32(rng, (K, N))
+    A16, B16 = oracle.f32_to_f16(A), oracle.f32_to_f16(B)    # includes overflow to inf and subnormals
+    want = np.zeros((M, N), np.uint16)
+    ref.ref_hgemm_host(M, N, K, A16, K, B16, N, want, N)     # GemmHostV1 (half), gemm_fp16_wmma.cu:75-90
+    got = oracle.hgemm_f16(A16, B16)
+    nan_w, nan_g = (want & 0x7fff) > 0x7c00, (got & 0x7fff) > 0x7c00   # inf - inf: any NaN payload is a NaN
+    assert np.array_equal(nan_w, nan_g) and np.array_equal(got[~nan_g], want[~nan_w])
+    Ab, Bb = oracle.f32_to_bf16(A), oracle.f32_to_bf16(np.ascontiguousarray(B.T))
+    wb = np.zeros((M, N), np.uint16)
+    assert ref.ref_linear_bf16(0, M, N, K, Ab, Bb, wb) == 0  # LinearNormalBf16, linear.cpp:137-151
+    gb = oracle.linear_bf16(Ab, Bb)
+    nan_w, nan_g = (wb & 0x7fff) > 0x7f80, (gb & 0x7fff) > 0x7f80
+    assert np.array_equal(nan_w, nan_g) and np.array_equal(gb[~nan_g], wb[~nan_w])
