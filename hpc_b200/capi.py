@@ -89,6 +89,8 @@ SIGNATURES = {
     "cuxb_linear_s8_s32_host": ([_vp, _i, _i, _i, _vp, _vp, _vp], _i),
     "cuxb_probe_hbm": ([_vp, _i, C.c_size_t, _i, C.POINTER(C.c_double)], _i),
     "cuxb_probe_fp32": ([_vp, _i, _i, C.POINTER(C.c_double)], _i),
+    "cuxb_probe_tensor": ([_vp, _i, _i, _i, C.POINTER(C.c_double), C.POINTER(C.c_double)], _i),
+    "cuxb_probe_nvlink": ([_vp, _i, _i, _i, C.c_size_t, _i, C.POINTER(C.c_double)], _i),
     "cuxb_kernel_occupancy": ([_vp, C.c_char_p, C.POINTER(_i), C.POINTER(C.c_double), C.POINTER(_i),
                                C.POINTER(_i)], _i),
 }
@@ -108,11 +110,8 @@ def lib():
         fn = getattr(L, name)
         fn.argtypes = args
         fn.restype = res
-    try:
-        L.cuxb_debug_set_cta_group.argtypes = [_i]
-        L.cuxb_debug_set_cta_group.restype = _i
-    except AttributeError:
-        pass
+    L.cuxb_debug_ctx_set.argtypes = [_vp, _i, _i]
+    L.cuxb_debug_ctx_set.restype = _i
     _lib = L
     return L
 
@@ -138,6 +137,11 @@ class Context:
     @property
     def sm_count(self):
         return lib().cuxb_ctx_sm_count(self._h)
+
+    def debug_set(self, what, value):
+        """Tuning / test hook of THIS context: what = "cta_group" | "group_m" | "wave_sync"."""
+        check(lib().cuxb_debug_ctx_set(self._h, {"cta_group": 0, "group_m": 1, "wave_sync": 2}[what], int(value)),
+              "cuxb_debug_ctx_set")
 
     def close(self):
         if self._h:
@@ -247,6 +251,19 @@ class Context:
         """Measured FP32 rate of the CUDA cores in TFLOP/s (scalar FFMA or packed FFMA2)."""
         v = C.c_double()
         check(lib().cuxb_probe_fp32(self._h, int(packed), reps, C.byref(v)), "cuxb_probe_fp32")
+        return v.value
+
+    def probe_tensor(self, kind=FLOAT16, data=1, reps=20):
+        """Measured tensor-pipe ceiling (TFLOP/s, TOP/s for INT8): (burst, mean over `reps` back-to-back launches)."""
+        b, m = C.c_double(), C.c_double()
+        check(lib().cuxb_probe_tensor(self._h, kind, int(data), reps, C.byref(b), C.byref(m)), "cuxb_probe_tensor")
+        return b.value, m.value
+
+    def probe_nvlink(self, peer_device, mode="bulk", depth=2, nbytes=256 << 20, reps=5):
+        """GB/s between peer_device's memory and this GPU: mode = "pull" | "push" | "memcpy" | "bulk"."""
+        v = C.c_double()
+        check(lib().cuxb_probe_nvlink(self._h, peer_device, {"pull": 0, "push": 1, "memcpy": 2, "bulk": 3}[mode], depth,
+                                      nbytes, reps, C.byref(v)), "cuxb_probe_nvlink")
         return v.value
 
     def occupancy(self, kernel):

@@ -102,6 +102,8 @@ struct cuxb_ctx {
   cuxb::TmaCacheEntry tma_cache[16];  // most recent TMA descriptors (encoding one costs microseconds)
   int tma_cache_n;
   int tma_cache_next;
+  // tuning / test hooks (cuxb_debug_ctx_set): per context, zero = library default
+  int dbg_cta_group, dbg_group_m, dbg_no_wave_sync;
   std::mutex *mu;      // serialises the *_host entry points (they share the staging buffers)
   std::mutex *tma_mu;  // guards the descriptor cache (taken inside kernels' entry points, never with mu's order reversed)
 };

@@ -120,7 +120,10 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
         if (e < total) {
           const int row = (int)e / n4, col4 = (int)e - row * n4;
           const float *sp = src + (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4;
-          asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+          // A coherent load: in a chain the upstream GPU is still writing other panels of this buffer
+          // while we read, so the non-coherent (.nc) path, which assumes memory that is read-only for
+          // the whole kernel, is not allowed here.  The acquire on the panel's flag above orders it.
+          asm volatile("ld.relaxed.sys.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
                        : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(sp) : "memory");
         }
       }
@@ -356,25 +359,27 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
       float *cp = p.C + (size_t)m * p.ldc + n;
       if (FAST) {
         float4 o;
+        // two separately rounded products and one add -- never contracted into an fma -- exactly as the
+        // tensor-core epilogue (umma_gemm.cu store8) and the CPU oracle's alpha*acc + beta*c do
         if (p.beta != 0.f) {
           const float4 c0 = *reinterpret_cast<const float4 *>(cp);
-          o.x = p.alpha * acc[i][h * 4 + 0] + p.beta * c0.x;
-          o.y = p.alpha * acc[i][h * 4 + 1] + p.beta * c0.y;
-          o.z = p.alpha * acc[i][h * 4 + 2] + p.beta * c0.z;
-          o.w = p.alpha * acc[i][h * 4 + 3] + p.beta * c0.w;
+          o.x = __fadd_rn(__fmul_rn(p.alpha, acc[i][h * 4 + 0]), __fmul_rn(p.beta, c0.x));
+          o.y = __fadd_rn(__fmul_rn(p.alpha, acc[i][h * 4 + 1]), __fmul_rn(p.beta, c0.y));
+          o.z = __fadd_rn(__fmul_rn(p.alpha, acc[i][h * 4 + 2]), __fmul_rn(p.beta, c0.z));
+          o.w = __fadd_rn(__fmul_rn(p.alpha, acc[i][h * 4 + 3]), __fmul_rn(p.beta, c0.w));
         } else {
-          o.x = p.alpha * acc[i][h * 4 + 0];
-          o.y = p.alpha * acc[i][h * 4 + 1];
-          o.z = p.alpha * acc[i][h * 4 + 2];
-          o.w = p.alpha * acc[i][h * 4 + 3];
+          o.x = __fmul_rn(p.alpha, acc[i][h * 4 + 0]);
+          o.y = __fmul_rn(p.alpha, acc[i][h * 4 + 1]);
+          o.z = __fmul_rn(p.alpha, acc[i][h * 4 + 2]);
+          o.w = __fmul_rn(p.alpha, acc[i][h * 4 + 3]);
         }
         *reinterpret_cast<float4 *>(cp) = o;
       } else if (m < p.M) {
 #pragma unroll
         for (int c = 0; c < 4; c++)
           if (n + c < p.N) {
-            float o = p.alpha * acc[i][h * 4 + c];
-            if (p.beta != 0.f) o += p.beta * cp[c];
+            float o = __fmul_rn(p.alpha, acc[i][h * 4 + c]);
+            if (p.beta != 0.f) o = __fadd_rn(o, __fmul_rn(p.beta, cp[c]));
             cp[c] = o;
           }
       }

@@ -31,190 +31,15 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "umma_ptx.cuh"
 
 namespace cuxb {
-
-enum { KIND_F16 = 0, KIND_BF16 = 1, KIND_S8 = 2 };
 
 constexpr int UG_BLOCK_M = 128;   // rows of A per CTA
 constexpr int UG_BLOCK_N = 256;   // columns per MMA (per CTA pair / per CTA when kCtaGroup==1)
 constexpr int UG_ROW_BYTES = 128; // bytes of K per shared-memory row (one swizzle span)
 constexpr int UG_THREADS = 256;
 constexpr int UG_GROUP_M = 8;
-
-// ------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-  return pred != 0;
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-// arrive on the barrier at this offset in the even (leader) CTA of the pair
-constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
-__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_local(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-  return ok != 0;
-}
-// Bounded wait: a pipeline bug must end in a trap (reported as a launch failure), never a hang.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin)
-    if (spin > 40000000u) __trap();
-}
-__device__ __forceinline__ unsigned long long global_timer_ns_() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-__device__ __forceinline__ unsigned int ld_acquire_gpu_u32(const unsigned int *p) {
-  unsigned int v;
-  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int *p) {
-  unsigned int v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys_u32(unsigned int *p, unsigned int v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned int atom_add_acq_rel_gpu(unsigned int *p, unsigned int v) {
-  unsigned int old;
-  asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
-  return old;
-}
-// spin until *p has reached `want` (wrap-around compare); a peer that never shows up is a launch error
-__device__ __forceinline__ void wait_sys_reached(const unsigned int *p, unsigned int want) {
-  const unsigned long long t0 = global_timer_ns_();
-  while ((int)(ld_acquire_sys_u32(p) - want) < 0)
-    if (global_timer_ns_() - t0 > 20000000000ull) __trap();
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-template <int CG>
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0, int c1) {
-  if (CG == 1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
-  } else {
-    // both CTAs of the pair run this; completion bytes are counted on the leader's barrier
-    asm volatile(
-        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1) : "memory");
-  }
-}
-template <int CG>
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
-  if (CG == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  } else {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-  }
-}
-template <int CG>
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
-  if (CG == 1)
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
-  else
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
-}
-template <int CG, int KIND>
-__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  if (KIND == KIND_S8) {
-    if (CG == 1)
-      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
-                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-    else
-      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
-                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-  } else {
-    if (CG == 1)
-      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-    else
-      asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                   ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-  }
-}
-// tcgen05.commit: the barrier is arrived on when every MMA issued so far by this thread has
-// completed.  With CG==2 the arrival is multicast to the same barrier offset in both CTAs.
-template <int CG>
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  if (CG == 1)
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-  else
-    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"((uint16_t)3) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-      : "r"(taddr) : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// Shared-memory matrix descriptor (sm_100 format): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46),
-// version=1 [46,48), layout type [61,64) with 2 = 128-byte swizzle.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
-  d |= 1ull << 46;
-  d |= 2ull << 61;
-  return d;
-}
-
-// Instruction descriptor: c_format [4,6) (1=f32, 2=s32), a_format [7,10), b_format [10,13)
-// (f16=0, bf16=1; signed int8=1), a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 [17,23),
-// M>>4 [24,29).
-template <int KIND, bool B_MN>
-__host__ __device__ constexpr uint32_t make_idesc(int mma_m, int mma_n) {
-  uint32_t d = 0;
-  const uint32_t fmt = (KIND == KIND_F16) ? 0u : 1u;  // bf16 = 1, signed int8 = 1
-  d |= ((KIND == KIND_S8) ? 2u : 1u) << 4;
-  d |= fmt << 7;
-  d |= fmt << 10;
-  d |= (B_MN ? 1u : 0u) << 16;
-  d |= (uint32_t)(mma_n >> 3) << 17;
-  d |= (uint32_t)(mma_m >> 4) << 24;
-  return d;
-}
 
 struct UmmaArgs {
   int M, N, K;         // problem
@@ -675,9 +500,6 @@ static int make_map(cuxb_ctx *ctx, CUtensorMap *map, const void *base, int ebyte
   return 0;
 }
 
-static int g_force_cta_group = 0;  // test hook: 0 = auto (2), 1 or 2
-static int g_group_m = UG_GROUP_M;  // test hook: rasterisation group height
-static int g_wave_sync = 1;          // soft per-wave rendezvous of the producers (test hook turns it off)
 
 template <int KIND, bool B_MN, int CT, int CG>
 static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, float alpha, const void *A, int lda,
@@ -702,7 +524,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   p.tiles_m = (int)div_up(M, UG_BLOCK_M * CG);
   p.tiles_n = (int)div_up(N, UG_BLOCK_N);
   p.k_blocks = (int)div_up(K, kBlockK);
-  p.group_m = g_group_m;
+  p.group_m = ctx->dbg_group_m > 0 ? ctx->dbg_group_m : UG_GROUP_M;
   p.wave_sync = nullptr;
   p.b_ready = nullptr, p.ready_target = 0;
   p.chain_local = nullptr, p.chain_up = nullptr, p.chain_down = nullptr, p.done_ctr = nullptr, p.done_target = 0;
@@ -752,7 +574,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   // 14-21 GB -> 8.8 GB, -4 % time at fixed clocks, +1 % under the power cap.  Short kernels lose more to
   // the counter's memset and the waits than the L2 hits return (8192^3 int8: 0.341 -> 0.375 ms), so
   // they run without it.
-  if (g_wave_sync && total >= 16 * clusters && p.k_blocks >= 128) {
+  if (!ctx->dbg_no_wave_sync && total >= 16 * clusters && p.k_blocks >= 128) {
     if (ctx->wave_sync == nullptr) CUXB_CUDA(cudaMalloc((void **)&ctx->wave_sync, 256));
     CUXB_CUDA(cudaMemsetAsync(ctx->wave_sync, 0, 4, st));
     p.wave_sync = ctx->wave_sync;
@@ -787,7 +609,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
 template <int KIND, bool B_MN, int CT>
 static int dispatch_cg(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, float alpha, const void *A, int lda,
                        const void *B, int ldb, float beta, void *C, int ldc) {
-  const int cg = g_force_cta_group ? g_force_cta_group : 2;
+  const int cg = ctx->dbg_cta_group ? ctx->dbg_cta_group : 2;
   if (cg == 1) return launch_umma<KIND, B_MN, CT, 1>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
   return launch_umma<KIND, B_MN, CT, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc);
 }
@@ -815,20 +637,17 @@ int umma_smem_bytes() { return UmmaCfg<2>::kSmemBytes; }
 
 using namespace cuxb;
 
-// test hook (not in cuxb.h): force the single-CTA (1) or paired-CTA (2) MMA variant; 0 = default
-CUXB_API int cuxb_debug_set_wave_sync(int on) {
-  g_wave_sync = on ? 1 : 0;
-  return 0;
-}
-CUXB_API int cuxb_debug_set_group_m(int g) {
-  if (g < 1 || g > 64) return CUXB_ERR_INVALID;
-  g_group_m = g;
-  return 0;
-}
-CUXB_API int cuxb_debug_set_cta_group(int cg) {
-  if (cg < 0 || cg > 2) return CUXB_ERR_INVALID;
-  g_force_cta_group = cg;
-  return 0;
+// Tuning / test hooks (not in cuxb.h).  They act on ONE context -- nothing process-wide is touched, so a
+// caller that flips one cannot change the kernels another context launches.
+//   what 0: MMA variant, value 0 = default (CTA pair), 1 = single CTA, 2 = CTA pair
+//   what 1: rasterisation group height (tile rows per L2 group), 0 = default, 1..64
+//   what 2: soft per-wave rendezvous of the TMA producers, value 1 = on (default), 0 = off
+CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
+  if (ctx == nullptr) return CUXB_ERR_INVALID;
+  if (what == 0 && value >= 0 && value <= 2) return ctx->dbg_cta_group = value, 0;
+  if (what == 1 && value >= 0 && value <= 64) return ctx->dbg_group_m = value, 0;
+  if (what == 2) return ctx->dbg_no_wave_sync = value ? 0 : 1, 0;
+  return CUXB_ERR_INVALID;
 }
 
 CUXB_API int cuxb_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, float alpha, const void *A,

@@ -297,9 +297,24 @@ int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *active_blocks_
  * copies; pocket-ai/eval/cuda/max_flops.cuh:11-94, timed fma chains).  Both calls allocate their own
  * buffers, run on the context's private stream, block until done and return the best of `reps` launches.
  * cuxb_probe_hbm: which = 0 read-only, 1 write-only, 2 copy (a copy of `bytes` counts as 2 x bytes moved);
- * use several times the 126 MB L2.  cuxb_probe_fp32: packed = 0 scalar FFMA, 1 packed FFMA2. */
+ * at least 64 MiB, use several times the 126 MB L2.  cuxb_probe_fp32: packed = 0 scalar FFMA, 1 packed FFMA2. */
 int cuxb_probe_hbm(cuxb_ctx *ctx, int which, size_t bytes, int reps, double *gb_per_s);
 int cuxb_probe_fp32(cuxb_ctx *ctx, int packed, int reps, double *tflops);
+/* Tensor-pipe ceiling (the tcgen05 counterpart of max_flops.cuh:11-94): CTA pairs issue tcgen05.mma
+ * 256 x 256 x 16 (kind CUXB_FLOAT16 / CUXB_BFLOAT16, TFLOP/s) or 256 x 256 x 32 (CUXB_INT8, TOP/s) back to
+ * back on operands resident in shared memory.  data = 0: all-zero operands, 1: pseudo-random operands (the
+ * data sets the power draw and, on a power-capped board, the clock).  *best_tflops = fastest single launch
+ * (burst); *mean_tflops = `reps` launches of about 4 ms each timed back to back (sustained when reps covers a
+ * second or more). */
+int cuxb_probe_tensor(cuxb_ctx *ctx, int kind, int data, int reps, double *best_tflops, double *mean_tflops);
+/* One entry of the NVLink pair matrix (pocket-ai/eval/cuda/device_query.hpp:134-186 lists peer access and
+ * topology; this measures it): GB/s between `peer_device`'s memory and this context's GPU.  mode 0 = a
+ * kernel on this GPU loads from the peer and stores locally; 1 = it loads locally and stores to the peer;
+ * 2 = cudaMemcpyPeerAsync peer -> here (copy engines); 3 = one thread per SM pulls with bulk async copies
+ * peer -> shared memory -> here through `depth` (1..12) 16 KiB buffers, the way the tensor GEMM's broadcast
+ * warp does.  Single process with both devices visible; `bytes` (multiple of 16 KiB, >= 16 MiB) is
+ * allocated on both GPUs for the duration of the call and peer access is enabled both ways. */
+int cuxb_probe_nvlink(cuxb_ctx *ctx, int peer_device, int mode, int depth, size_t bytes, int reps, double *gb_per_s);
 
 #ifdef __cplusplus
 }

@@ -60,6 +60,19 @@ def test_sgemm_float_fill_tolerance(shape):
     assert ok, d
 
 
+@pytest.mark.parametrize("shape", [(128, 128, 1), (130, 70, 1)])   # vectorised and guarded epilogues
+def test_sgemm_float_fill_k1_beta_bit_exact(shape):
+    # K = 1: there is no summation order to differ in, so with alpha = 1 the result must equal
+    # GemmHostV0's fl(fl(beta*c) + fl(a*b)) bit for bit on arbitrary floats -- which it only does if the
+    # epilogue rounds alpha*acc and beta*c separately (no fma contraction).
+    M, N, K = shape
+    A, B, C = dg.uniform_fill((M, K), tag=14), dg.uniform_fill((K, N), tag=15), dg.uniform_fill((M, N), tag=16)
+    for beta in (0.75, -3.0, 1.0 / 3.0):
+        got = run_sgemm(A, B, C, 1.0, beta)
+        want = oracle.gemm_f32(A, B, C, 1.0, beta, order="v0")
+        assert np.array_equal(bits32(got), bits32(want)), beta
+
+
 def test_sgemm_golden_and_leading_dimensions():
     for name in ("gemm_int", "gemm_flt"):
         got = run_sgemm(G[name + "_A"], G[name + "_B"], G[name + "_C0"], 1.0, 3.0)
@@ -123,9 +136,9 @@ def run_hgemm(A16, B16, C0=None, alpha=1.0, beta=0.0, c_f32=False):
 
 @pytest.fixture(params=[2, 1], ids=["cta_pair", "single_cta"])
 def cta_group(request):
-    capi.lib().cuxb_debug_set_cta_group(request.param)
+    ctx().debug_set("cta_group", request.param)   # per context: no other context's kernels change
     yield request.param
-    capi.lib().cuxb_debug_set_cta_group(0)
+    ctx().debug_set("cta_group", 0)
 
 
 @pytest.mark.parametrize("shape", [(128, 128, 64), (256, 256, 256), (512, 768, 1024), (200, 136, 72), (1, 8, 8),
@@ -192,6 +205,15 @@ def test_hgemm_full_size_16384_sampled_rows():
     B16 = host(dB.view(torch.int16), np.uint16)
     want = oracle.hgemm_f16(A16, B16, c_f32=True, threads=8)
     assert np.array_equal(host(dC[rows]), want)
+    # the same with fp16 OUTPUT, cux's convention (gemm.cu:266-269) and what bench.py times: at K = 16384
+    # |acc| goes far beyond 2048, so the final round-to-nearest-even matters on most elements
+    dC16 = torch.zeros((n, n), dtype=torch.float16, device="cuda")
+    ctx().hgemm_f16(n, n, n, 1.0, dA.data_ptr(), n, dB.data_ptr(), n, 0.0, dC16.data_ptr(), n, capi.FLOAT16)
+    sync()
+    want16 = oracle.hgemm_f16(A16, B16, threads=8)
+    assert np.array_equal(host(dC16[rows].view(torch.int16), np.uint16), want16)
+    assert np.abs(want).max() > 2048
+    assert torch.equal(dC16, dC.to(torch.float16))   # every element: one RNE of the fp32 accumulator
     # checksum of checksums: sum_j C[i,j] == A[i,:] . rowsum(B)  (exact in fp64 for these integers)
     rs = dB.double().sum(dim=1)
     lhs = dC.double().sum(dim=1)

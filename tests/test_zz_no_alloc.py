@@ -12,10 +12,15 @@ The file is named test_zz_* so that pytest collects it after every other test: i
 after the rest of the suite.  Integer results are compared bit for bit (the tolerance the other
 integer tests use), on two calls in a row that reuse the same scratch.
 """
+import os
+import subprocess
+import sys
+
 import numpy as np
 import pytest
 import torch
 
+import oracle
 from hpc_b200 import capi
 from hpc_b200 import datagen as dg
 
@@ -77,3 +82,55 @@ def test_noalloc_scan_at_its_size_limit_and_beyond():
     assert capi.lib().cuxb_scan_i32_noalloc(0, 8, 0, out.data_ptr(), 0) != 0
     assert capi.lib().cuxb_scan_i32_noalloc(0, 0, 0, 0, 0) == 0  # empty input is a no-op
     ctx.close()
+
+
+def _free_bytes():
+    """Free device memory as the driver reports it (cudaMemGetInfo: device-wide, not torch's cache)."""
+    return torch.cuda.mem_get_info(0)[0]
+
+
+def test_noalloc_scan_matches_the_oracle_and_allocates_nothing():
+    """The property the entry point exists for: after the first call on a device (which loads the kernel
+    and resolves the scratch array's address), calls leave the driver's free-memory figure untouched --
+    and the result is the reference recurrence itself, not just "what the other entry point gives"."""
+    torch.cuda.set_device(0)
+    x_h = dg.int_fill(2_000_003, -2, 2, np.int32, tag=21)
+    x = torch.from_numpy(x_h).cuda()
+    out = torch.empty_like(x)
+    st = torch.cuda.current_stream().cuda_stream
+    L = capi.lib()
+    capi.check(L.cuxb_scan_i32_noalloc(st, x.numel(), x.data_ptr(), out.data_ptr(), 11), "first call")
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), oracle.scan_i32(x_h, seed=11))
+    before = _free_bytes()
+    for i in range(100):
+        capi.check(L.cuxb_scan_i32_noalloc(st, x.numel() - i, x.data_ptr(), out.data_ptr(), i), "call %d" % i)
+    torch.cuda.synchronize()
+    assert _free_bytes() == before, "cuxb_scan_i32_noalloc changed the amount of free device memory"
+    assert np.array_equal(out.cpu().numpy()[:x.numel() - 99], oracle.scan_i32(x_h[:x.numel() - 99], seed=99))
+
+
+_FRESH = r"""
+import sys
+import numpy as np, torch
+sys.path.insert(0, %r)
+import oracle
+from hpc_b200 import capi, datagen as dg
+# no capi.Context anywhere in this process: the entry point has to work without one
+torch.cuda.set_device(0)
+x_h = dg.int_fill(1_000_001, -2, 2, np.int32, tag=33)
+x = torch.from_numpy(x_h).cuda()
+out = torch.empty_like(x)
+for seed in (4, -4):   # two calls in a row
+    rc = capi.lib().cuxb_scan_i32_noalloc(torch.cuda.current_stream().cuda_stream, x.numel(), x.data_ptr(), out.data_ptr(), seed)
+    assert rc == 0, capi.lib().cuxb_last_error_string()
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), oracle.scan_i32(x_h, seed=seed))
+print("fresh-process ok")
+"""
+
+
+def test_noalloc_scan_in_a_process_that_never_creates_a_context():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", _FRESH % root], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "fresh-process ok" in r.stdout, r.stdout + r.stderr

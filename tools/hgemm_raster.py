@@ -19,8 +19,8 @@ else:
 for g in [int(x) for x in (sys.argv[1:] or ["8", "4", "6", "12", "16", "8"])]:
     sync = 1 if g < 0 else 0      # a negative group height = that height with the soft wave rendezvous on
     g = abs(g)
-    L.cuxb_debug_set_wave_sync(sync)
-    L.cuxb_debug_set_group_m(g)
+    ctx.debug_set("wave_sync", sync)
+    ctx.debug_set("group_m", g)
     for _ in range(int(os.environ.get('WARM', '3'))): f()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -32,10 +32,10 @@ assert np.array_equal(dC.cpu().numpy(), oracle.gemm_f32(A2, B2, C2, 1.0, 0.0))
 A16, B16 = oracle.f32_to_f16(A), oracle.f32_to_f16(B)
 dA, dB = dev(A16), dev(B16); dC = torch.zeros((M, N), dtype=torch.int16, device="cuda")
 for cg in (2, 1):
-    capi.lib().cuxb_debug_set_cta_group(cg)
+    ctx.debug_set("cta_group", cg)
     ctx.hgemm_f16(M, N, K, 1.0, dA.data_ptr(), K, dB.data_ptr(), N, 0.0, dC.data_ptr(), N, capi.FLOAT16); torch.cuda.synchronize()
     assert np.array_equal(dC.cpu().numpy().view(np.uint16), oracle.hgemm_f16(A16, B16))
-capi.lib().cuxb_debug_set_cta_group(0)
+ctx.debug_set("cta_group", 0)
 A8, B8 = dg.int_fill((130, 64), -128, 127, np.int8, tag=9), dg.int_fill((264, 64), -128, 127, np.int8, tag=10)
 dA, dB = dev(A8), dev(B8); dC = torch.zeros((130, 264), dtype=torch.int32, device="cuda")
 ctx.linear_s8(130, 264, 64, dA.data_ptr(), dB.data_ptr(), dC.data_ptr()); torch.cuda.synchronize()
