@@ -57,7 +57,7 @@ def build(force=False, verbose=True, extra_flags=(), out=None, build_dir=None):
     with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
         list(ex.map(run, jobs))
     if force or jobs or _stale(SO, objs):
-        run([NVCC, "-shared", "-o", SO] + objs + ["-lcudart_static", "-ldl", "-lpthread", "-lrt"])
+        run([NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", SO] + objs + ["-lcudart_static", "-ldl", "-lpthread", "-lrt"])
     return SO
 
 

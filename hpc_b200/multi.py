@@ -108,6 +108,40 @@ class PeerExchange:
         out.ptrs = [int(p) for p in out.handle.buffer_ptrs]
         return out
 
+    def route(self, ctx, B, mode):
+        """How B reaches this rank in the fused-broadcast GEMMs.  Allocates a symmetric copy of B (the root
+        fills its instance from B) and, for "chain", the symmetric flag buffers.  Returns an object with
+          .b_up / .b_local   the pointers to pass as b_root / b_local (bt_root / bt_local)
+          .activate()        select this route on ctx (host-side state; call before each step)
+          .clear_local()     zero this rank's copy (tests: prove that a call really delivered B)
+          .local_equals(B)   this rank's copy == B
+          .describe          one line for the bench output"""
+        import torch
+        import torch.distributed as dist
+        from . import capi
+        r, w = self.rank, self.world
+        R = self.symmetric_like(B)
+        if r == 0:
+            R.tensor.copy_(B)
+        R.b_local = R.ptrs[r]
+        src, up, down = chain_plan(w, r, mode)
+        R.b_up = R.ptrs[src if src is not None else 0]
+        if mode == "chain" and w > 2:
+            F = self.symmetric_like(torch.empty(capi.MG_CHAIN_FLAGS_BYTES // 4, dtype=torch.int32, device=B.device))
+            F.tensor.zero_()
+            R.flags = F
+            chain = (F.ptrs[r], F.ptrs[up] if up is not None else 0, F.ptrs[down] if down is not None else 0)
+            R.activate = (lambda: ctx.mg_set_chain(*chain)) if r > 0 else (lambda: None)
+            R.describe = "from the rank before it (chain: each GPU sends B once)"
+        else:
+            R.activate = lambda: ctx.mg_set_chain(0, 0, 0)
+            R.describe = "straight from rank 0 (star)"
+        R.clear_local = (lambda: R.tensor.zero_()) if r > 0 else (lambda: None)
+        R.local_equals = lambda Bt: bool(torch.equal(R.tensor, Bt))
+        torch.cuda.synchronize()
+        dist.barrier()
+        return R
+
     def chain(self, ctx, b_like):
         """Set up the chained broadcast (cuxb_mg_set_chain) for ctx: a symmetric copy of B and symmetric
         flags; rank r pulls from rank r - 1.  Returns (bsym, upstream_ptr): bsym.tensor is this rank's B

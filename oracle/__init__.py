@@ -61,15 +61,7 @@ def lib():
     return L
 
 
-def ref():
-    """The reference's own host functions (None when oracle/_ref was never built)."""
-    global _ref, _ref_tried
-    if _ref_tried:
-        return _ref
-    _ref_tried = True
-    path = os.path.join(_HERE, "_ref", "libcuxref.so")
-    if not os.path.exists(path):
-        return None
+def _bind_ref(path):
     R = C.CDLL(path)
     R.ref_cux_gemm.argtypes = [_i, _i, _i, _i, _f, _f32p, _i, _f32p, _i, _f, _f32p, _i]
     R.ref_cux_dot_v0.argtypes = [_i, _f32p, _f32p, _f32p]
@@ -83,8 +75,33 @@ def ref():
     R.ref_linear_bf16.argtypes = [_i, _i, _i, _i, _u16p, _u16p, _u16p]
     R.ref_linear_f32.argtypes = [_i, _i, _i, _f32p, _f32p, _f32p]
     R.ref_scan_f32.argtypes = [_i, _f32p, _i, _f32p]
-    _ref = R
     return R
+
+
+def ref():
+    """The reference's own host functions, PARITY build (None when oracle/_ref was never built)."""
+    global _ref, _ref_tried
+    if _ref_tried:
+        return _ref
+    _ref_tried = True
+    path = os.path.join(_HERE, "_ref", "libcuxref.so")
+    if not os.path.exists(path):
+        return None
+    _ref = _bind_ref(path)
+    return _ref
+
+
+_ref_fast = None
+
+
+def ref_fast():
+    """The same functions from the -O3 build (oracle/build.py): for TIMING only -- floating-point
+    contraction is allowed there, so nothing is ever compared against it.  Falls back to ref()."""
+    global _ref_fast
+    if _ref_fast is None:
+        path = os.path.join(_HERE, "_ref", "libcuxref_fast.so")
+        _ref_fast = _bind_ref(path) if os.path.exists(path) else ref()
+    return _ref_fast
 
 
 # --------------------------------------------------------------------------

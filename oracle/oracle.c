@@ -202,37 +202,53 @@ ORC_API void orc_hgemm_f16(int M, int N, int K, float alpha, const uint16_t *A, 
                            const uint16_t *B, int ldb, float beta, void *C, int ldc,
                            int c_is_f32, int threads) {
   (void)threads;
-  /* Convert once; the conversion is exact so this does not change results. */
-  float *Bf = (float *)malloc((size_t)K * N * sizeof(float));
-  for (int k = 0; k < K; ++k)
-    for (int j = 0; j < N; ++j) Bf[(size_t)k * N + j] = orc_f16_to_f32(B[(size_t)k * ldb + j]);
-#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(static)
-  for (int i = 0; i < M; ++i) {
-    float *Af = (float *)malloc((size_t)K * sizeof(float));
-    for (int k = 0; k < K; ++k) Af[k] = orc_f16_to_f32(A[(size_t)i * lda + k]);
-    for (int j = 0; j < N; ++j) {
-      float acc = 0.f;
+  /* Same arithmetic as the reference loop -- for every (i, j): acc = 0; acc += a[i,k] * b[k,j] for k = 0..K-1 in
+   * increasing order, each product and each sum rounded to fp32 -- but walked column BLOCK by column block with
+   * k outside j, so that B is read along its rows.  The sequence of operations that produces any one C[i,j] is
+   * unchanged, so the results are bit-identical to the i-j-k walk (tests/test_oracle_vs_ref.py pins that against
+   * the reference's own function); it is only ~20x faster, which lets the GPU tests check more rows.
+   * The fp16 -> fp32 conversions are exact, so doing them once per block changes nothing either. */
+  enum { JB = 256 };
+  const int nblk = (N + JB - 1) / JB;
+  float *Af = (float *)malloc((size_t)(M > 0 ? M : 1) * (K > 0 ? K : 1) * sizeof(float));
+  for (int i = 0; i < M; ++i)
+    for (int k = 0; k < K; ++k) Af[(size_t)i * K + k] = orc_f16_to_f32(A[(size_t)i * lda + k]);
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic, 1)
+  for (int jb = 0; jb < nblk; ++jb) {
+    const int j0 = jb * JB, jn = (N - j0 < JB) ? N - j0 : JB;
+    float *Bf = (float *)malloc((size_t)(K > 0 ? K : 1) * JB * sizeof(float));
+    for (int k = 0; k < K; ++k)
+      for (int j = 0; j < jn; ++j) Bf[(size_t)k * JB + j] = orc_f16_to_f32(B[(size_t)k * ldb + j0 + j]);
+    for (int i = 0; i < M; ++i) {
+      float acc[JB];
+      for (int j = 0; j < jn; ++j) acc[j] = 0.f;
       for (int k = 0; k < K; ++k) {
-        float p = Af[k] * Bf[(size_t)k * N + j];
-        acc += p;
+        const float a = Af[(size_t)i * K + k];
+        const float *brow = Bf + (size_t)k * JB;
+        for (int j = 0; j < jn; ++j) {
+          float p = a * brow[j];
+          acc[j] += p;
+        }
       }
-      float r;
-      if (beta == 0.0f) {
-        r = alpha * acc;
-      } else {
-        float c0 = c_is_f32 ? ((float *)C)[(size_t)i * ldc + j]
-                            : orc_f16_to_f32(((uint16_t *)C)[(size_t)i * ldc + j]);
-        float t0 = alpha * acc, t1 = beta * c0;
-        r = t0 + t1;
+      for (int j = 0; j < jn; ++j) {
+        float r;
+        if (beta == 0.0f) {
+          r = alpha * acc[j];
+        } else {
+          float c0 = c_is_f32 ? ((float *)C)[(size_t)i * ldc + j0 + j]
+                              : orc_f16_to_f32(((uint16_t *)C)[(size_t)i * ldc + j0 + j]);
+          float t0 = alpha * acc[j], t1 = beta * c0;
+          r = t0 + t1;
+        }
+        if (c_is_f32)
+          ((float *)C)[(size_t)i * ldc + j0 + j] = r;
+        else
+          ((uint16_t *)C)[(size_t)i * ldc + j0 + j] = orc_f32_to_f16(r);
       }
-      if (c_is_f32)
-        ((float *)C)[(size_t)i * ldc + j] = r;
-      else
-        ((uint16_t *)C)[(size_t)i * ldc + j] = orc_f32_to_f16(r);
     }
-    free(Af);
+    free(Bf);
   }
-  free(Bf);
+  free(Af);
 }
 
 /* ------------------------------------------------------------------------ */

@@ -193,3 +193,32 @@ def test_probes_report_plausible_ceilings():
     assert 40 < f1 < 80 and 40 < f2 < 80 and f2 >= 0.95 * f1, (f1, f2)
     with pytest.raises(capi.CuxbError):
         c.probe_hbm("read", 1000, 3)          # too small / not a multiple of 16
+    with pytest.raises(capi.CuxbError):
+        c.probe_hbm("read", 1 << 20, 3)       # below 64 MiB the loop would barely run: rejected, not mis-reported
+
+
+def test_tensor_probe_reports_plausible_ceilings():
+    """cuxb_probe_tensor: tcgen05.mma on shared-memory-resident operands (the tensor-pipe counterpart of
+    max_flops.cuh:11-94).  Dense fp16 is 2250 TFLOP/s nominal, int8 twice that; a power-capped board sits below."""
+    c = ctx()
+    b16, m16 = c.probe_tensor(capi.FLOAT16, data=1, reps=10)
+    bz, _ = c.probe_tensor(capi.BFLOAT16, data=0, reps=5)
+    b8, m8 = c.probe_tensor(capi.INT8, data=1, reps=10)
+    assert 1000 < m16 <= b16 * 1.02 and b16 < 2400, (b16, m16)
+    assert 1000 < bz < 2400, bz
+    assert 2000 < m8 <= b8 * 1.02 and b8 < 4800, (b8, m8)
+    with pytest.raises(capi.CuxbError):
+        c.probe_tensor(capi.FLOAT32)
+
+
+def test_nvlink_probe_pair():
+    """cuxb_probe_nvlink between GPU 0 and GPU 1 (needs two GPUs): every mode lands between PCIe-class and the
+    900 GB/s one direction of NVLink 5 can carry."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    c = ctx()
+    for mode, depth in (("pull", 0), ("push", 0), ("memcpy", 0), ("bulk", 2), ("bulk", 8)):
+        v = c.probe_nvlink(1, mode, depth, 256 << 20, 3)
+        assert 100 < v < 950, (mode, depth, v)
+    with pytest.raises(capi.CuxbError):
+        c.probe_nvlink(0, "pull")             # the context's own GPU is not a peer
