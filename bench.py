@@ -427,9 +427,13 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
                 if data == "int":
                     rep["rows"] = bool(np.array_equal(got, want))
                 else:
+                    # one fp16 ulp of the output + the fp32 accumulation-order noise of a K-long sum of O(1) terms
+                    # (8 eps32 K: near-zero outputs carry that noise in full, far above their own ulp)
                     g, w = oracle.f16_to_f32(got), oracle.f16_to_f32(want)
-                    rep["rows"] = bool(np.all(np.abs(g - w) <= 2.0 ** -10 * np.abs(w) + 1e-3))
-                    rep["max_abs_err"], rep["tolerance"] = float(np.max(np.abs(g - w))), "2^-10 |w| + 1e-3 (one fp16 ulp)"
+                    bad = np.abs(g - w) > 2.0 ** -10 * np.abs(w) + 8 * 2.0 ** -24 * n
+                    rep["rows"] = not bool(bad.any())
+                    rep["mismatches"], rep["elements"] = int(bad.sum()), int(bad.size)
+                    rep["max_abs_err"], rep["tolerance"] = float(np.max(np.abs(g - w))), "2^-10 |w| + 8 eps32 K"
             else:
                 hA = A[rows].cpu().numpy()
                 want = oracle.linear_s8(hA, hB, threads=8)
