@@ -163,7 +163,7 @@ def _gen_float(torch, shape, kind, dtype, seed):
     return (torch.rand(shape, device="cuda", generator=g, dtype=torch.float32) * 2 - 1).to(dtype)
 
 
-def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain", share=1, data="int"):
+def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="mcast", share=1, data="int"):
     """Device-resident inputs for this rank's part of `name` plus the callables that run it.
     share: how many ranks the named size is divided over (world for strong scaling, 1 for weak).
     data: "int" = the reference's integer-valued fills; "float" = the second data set of SURVEY 8(d)."""
@@ -351,14 +351,17 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
         fused_C = C
         if world > 1 and peers is not None:
             # B lives on rank 0 only; every other rank's GEMM kernel gets it over NVLink while multiplying
-            routes = {}
-            for mode in ([bcast] + [x for x in ("chain", "star") if x != bcast and world > 2]):
+            routes, order = {}, [bcast] + [x for x in ("mcast", "chain", "star") if x != bcast]
+            if world == 2:
+                order = [x for x in order if x != "chain"]      # with one receiver the chain is the star
+            for mode in order:
                 try:
                     routes[mode] = peers.route(ctx, B, mode)
-                except Exception as ex:
+                except Exception as ex:                          # e.g. no multicast on this box: reported below
                     routes[mode] = ex
-            if isinstance(routes[bcast], Exception):
-                raise routes[bcast]
+            W.bcast_unavailable = {k: str(v)[:160] for k, v in routes.items() if isinstance(v, Exception)}
+            bcast = next(m for m in order if not isinstance(routes[m], Exception))   # the first route that exists
+            W.bcast = bcast
             torch.cuda.synchronize()
             dist.barrier()
             is_root = rank == 0
@@ -388,6 +391,8 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
                             % ((B.numel() * B.element_size()) >> 20, routes[bcast].describe))
             W.keep.append(routes)
             W.bcast_bytes = B.numel() * B.element_size()
+            if W.bcast_unavailable:
+                W.collective += "; unavailable here: %s" % W.bcast_unavailable
 
         def verify():
             """Sampled rows bit-exact (integer fill) or within the stated tolerance (float fill) vs the oracle;
@@ -395,7 +400,7 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
             import oracle
             rep = {"how": "sampled rows vs oracle: bit-exact" if data == "int" or name == "linear_s8" else "sampled rows vs oracle within tolerance"}
             if world > 1 and peers is not None and rank != 0:
-                W.routes[bcast].clear_local()      # the check must see THIS call's delivery, not an earlier one
+                W.routes[W.bcast].clear_local()    # the check must see THIS call's delivery, not an earlier one
             torch.cuda.synchronize()
             if dist is not None:
                 dist.barrier()
@@ -443,7 +448,7 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain"
                                                             (A.double() @ B.double().sum(dim=0)).to(torch.int64)))
             rep["rows_checked"] = rows
             if world > 1 and peers is not None:
-                rep["b_delivered"] = True if rank == 0 else bool(W.routes[bcast].local_equals(B))
+                rep["b_delivered"] = True if rank == 0 else bool(W.routes[W.bcast].local_equals(B))
                 C2 = torch.empty_like(C)
                 plain(B.data_ptr(), C2.data_ptr())
                 torch.cuda.synchronize()
@@ -1013,9 +1018,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: exchange fused into the kernel over peer memory (default) or a NCCL collective after it")
-    ap.add_argument("--bcast", default="chain", choices=["chain", "star"],
-                    help="N>1 GEMMs, how B reaches the non-root ranks: chain = rank r pulls from rank r-1's copy (every GPU "
-                         "sends B once), star = everybody pulls from the root")
+    ap.add_argument("--bcast", default="mcast", choices=["mcast", "chain", "star"],
+                    help="N>1 GEMMs, how B reaches the non-root ranks: mcast = the root stores it once to an NVSwitch "
+                         "multicast address (default; falls back to chain where there is no multicast), chain = rank r pulls "
+                         "from rank r-1's copy (every GPU sends B once), star = everybody pulls from the root")
     ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
                     help="N>1.  strong (default): the named size is the whole job, each GPU takes 1/N of the elements "
                          "(vectors) or of the rows of A and C (GEMMs); weak: the named size PER GPU")
@@ -1050,8 +1056,6 @@ def main():
             peers = multi.PeerExchange(dist, torch.device("cuda", local))
         except Exception as ex:  # reported in the JSON line, never silent
             peers_note = "peer-memory rendezvous failed (%s): NCCL collective used instead" % str(ex)[:200]
-    if world <= 2:
-        args.bcast = "star"       # with one receiver every route is the same: it pulls from the root
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()

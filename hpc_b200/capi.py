@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("CUXB_LIB_PATH") or os.path.join(_HERE, "libcuxb.so")
 FLOAT32, INT32, FLOAT16, INT8, BFLOAT16 = 0, 1, 2, 3, 4
 MG_EXCHANGE_BYTES = 256       # CUXB_MG_EXCHANGE_BYTES
 MG_CHAIN_FLAGS_BYTES = 16640  # CUXB_MG_CHAIN_FLAGS_BYTES
+MG_MCAST_FLAGS_BYTES = 16640  # CUXB_MG_MCAST_FLAGS_BYTES
 
 
 class CuxbError(RuntimeError):
@@ -71,6 +72,7 @@ SIGNATURES = {
     "cuxb_mg_linear_bf16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i], _i),
     "cuxb_mg_linear_f16_f32acc": ([_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i], _i),
     "cuxb_mg_set_chain": ([_vp, _vp, _vp, _vp], _i),
+    "cuxb_mg_set_multicast": ([_vp, _i, _i, _vp, _vp, _vp], _i),
     "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
@@ -140,7 +142,7 @@ class Context:
 
     def debug_set(self, what, value):
         """Tuning / test hook of THIS context: what = "cta_group" | "group_m" | "wave_sync"."""
-        check(lib().cuxb_debug_ctx_set(self._h, {"cta_group": 0, "group_m": 1, "wave_sync": 2}[what], int(value)),
+        check(lib().cuxb_debug_ctx_set(self._h, {"cta_group": 0, "group_m": 1, "wave_sync": 2, "mc_group": 3}[what], int(value)),
               "cuxb_debug_ctx_set")
 
     def close(self):
@@ -233,6 +235,10 @@ class Context:
     def mg_set_chain(self, flags_local, flags_up, flags_down):
         check(lib().cuxb_mg_set_chain(self._h, flags_local or None, flags_up or None, flags_down or None),
               "cuxb_mg_set_chain")
+
+    def mg_set_multicast(self, world, rank, flags_local, flags_mc, b_mc):
+        check(lib().cuxb_mg_set_multicast(self._h, world, rank, flags_local or None, flags_mc or None, b_mc or None),
+              "cuxb_mg_set_multicast")
 
     def convert(self, n, src, src_dtype, dst, dst_dtype, stream=0):
         check(lib().cuxb_convert(self._h, stream, n, src, src_dtype, dst, dst_dtype), "cuxb_convert")

@@ -81,6 +81,16 @@ struct cuxb_ctx {
   unsigned int bcast_done_total;   // chained broadcast: panels published so far (all calls)
   unsigned int *chain_local;       // chained broadcast flags (cuxb_mg_set_chain), peer-mapped
   const unsigned int *chain_up, *chain_down;
+  // NVSwitch multicast broadcast (cuxb_mg_set_multicast): peer- / multicast-mapped flag buffers
+  int mc_world, mc_rank;
+  unsigned int *mc_flags_local, *mc_flags_mc;
+  void *mc_b;                      // multicast address of the ranks' copies of B
+  // call counters (the call epoch; same on every rank), one per flags buffer this context has been given:
+  // a caller may keep several broadcasts (several B's, each with its own flags) alive and switch between them
+  struct { const void *flags; unsigned int calls; } mc_tab[8];
+  int mc_cur;                      // index into mc_tab of the active flags
+  unsigned int mc_done_total;      // receiver: tensor-GEMM CTAs launched so far in multicast mode (all calls)
+  unsigned int sg_mc_done_total;   // the same for the SGEMM (its device-side counter is separate)
   // sgemm split-K: parked accumulators + per-tile tickets
   void *sg_scratch;
   size_t sg_scratch_bytes;
@@ -103,7 +113,7 @@ struct cuxb_ctx {
   int tma_cache_n;
   int tma_cache_next;
   // tuning / test hooks (cuxb_debug_ctx_set): per context, zero = library default
-  int dbg_cta_group, dbg_group_m, dbg_no_wave_sync;
+  int dbg_cta_group, dbg_group_m, dbg_no_wave_sync, dbg_mc_group;
   std::mutex *mu;      // serialises the *_host entry points (they share the staging buffers)
   std::mutex *tma_mu;  // guards the descriptor cache (taken inside kernels' entry points, never with mu's order reversed)
 };

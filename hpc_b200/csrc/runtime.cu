@@ -221,6 +221,42 @@ CUXB_API int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *fla
   return 0;
 }
 
+// NVSwitch multicast all-gather for the cuxb_mg_*gemm / cuxb_mg_linear_* calls of this context (see cuxb.h).
+CUXB_API int cuxb_mg_set_multicast(cuxb_ctx *ctx, int world, int rank, void *flags_local, void *flags_mc, void *b_mc) {
+  CUXB_REQUIRE(ctx != nullptr, CUXB_ERR_INVALID, "cuxb_mg_set_multicast: null context");
+  if (flags_local == nullptr) {   // off
+    ctx->mc_flags_local = ctx->mc_flags_mc = nullptr;
+    ctx->mc_b = nullptr;
+    ctx->mc_world = 0, ctx->mc_rank = 0;
+    return 0;
+  }
+  CUXB_REQUIRE(world >= 3 && world <= 8 && rank >= 0 && rank < world, CUXB_ERR_INVALID,
+               "cuxb_mg_set_multicast: world=%d rank=%d (3..8 ranks; with two, the one receiver simply pulls from the root)",
+               world, rank);
+  CUXB_REQUIRE(rank == 0 || (flags_mc != nullptr && b_mc != nullptr), CUXB_ERR_INVALID,
+               "cuxb_mg_set_multicast: a receiving rank needs the multicast addresses of the flags and of the copies of B");
+  CUXB_REQUIRE((((uintptr_t)flags_local | (uintptr_t)flags_mc) & 3) == 0 && ((uintptr_t)b_mc & 15) == 0, CUXB_ERR_INVALID,
+               "cuxb_mg_set_multicast: flag buffers must be 4-byte aligned, the copies of B 16-byte aligned");
+  // the call number belongs to the flags: it continues when the same flags are selected again, and new
+  // (zeroed) flags start at 1.  Eight flag buffers are remembered per context; beyond that the oldest
+  // entry is reused (its flags must then not be selected again).
+  int slot = -1;
+  for (int i = 0; i < 8; i++)
+    if (ctx->mc_tab[i].flags == flags_local) slot = i;
+  if (slot < 0) {
+    for (int i = 0; i < 8 && slot < 0; i++)
+      if (ctx->mc_tab[i].flags == nullptr) slot = i;
+    if (slot < 0) slot = (ctx->mc_cur + 1) % 8;
+    ctx->mc_tab[slot].flags = flags_local, ctx->mc_tab[slot].calls = 0;
+  }
+  ctx->mc_cur = slot;
+  ctx->mc_world = world, ctx->mc_rank = rank;
+  ctx->mc_flags_local = (unsigned int *)flags_local;
+  ctx->mc_flags_mc = (unsigned int *)flags_mc;
+  ctx->mc_b = b_mc;
+  return 0;
+}
+
 CUXB_API int cuxb_stream_create(void **s) {
   CUXB_REQUIRE(s, CUXB_ERR_INVALID, "null");
   cudaStream_t st;

@@ -61,7 +61,20 @@ struct SgemmArgs {
   const unsigned int *chain_up, *chain_down;
   unsigned int *done_ctr;
   unsigned int done_target;
+  // NVSwitch multicast all-gather (cuxb_mg_set_multicast; the protocol is described in umma_gemm.cu):
+  // mc_mode 2 = receiving rank, whose copy CTAs pull the rows of B this rank owns (every (world-1)-th row)
+  // from the root and store them to the multicast address Bdst -- every rank's copy at once -- and whose
+  // other CTAs wait, k-panel by k-panel, for the world-1 announcements in their own instance of the flags.
+  int mc_mode;
+  unsigned int mc_epoch;
+  float *Bdst;
+  unsigned int *mc_flags_local, *mc_flags_mc;
+  int mc_world, mc_rank;
+  unsigned int *mc_done_ctr;
+  unsigned int mc_done_target;
 };
+constexpr int kSgMcMaxGroups = 512;   // same flag layout as umma_gemm.cu (kMcMaxGroups, kMcDoneBase)
+constexpr int kSgMcDoneBase = 4100;   // same flag layout as umma_gemm.cu's kMcDoneBase
 
 constexpr int kSgPullInFlight = 16;  // 16-byte loads in flight per thread: 64 KiB per copy CTA over NVLink
 constexpr int kSgPullPanelK = 128;   // rows of B per readiness flag
@@ -94,8 +107,17 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
   const int n4 = p.N >> 2;
   const int stride = p.n_copy * SG_THREADS;
   const float *src = p.Bsrc;
-  float *dst = const_cast<float *>(p.B);
+  float *dst = p.mc_mode == 2 ? p.Bdst : const_cast<float *>(p.B);
+  const int nr = p.mc_mode == 2 ? p.mc_world - 1 : 1, ro = p.mc_mode == 2 ? p.mc_rank - 1 : 0;   // rows we own: ro + nr * j
   unsigned int epoch = 0;
+  if (p.mc_mode == 2) {
+    // our stores land in every rank's copy: nothing of the previous call may be overwritten before every
+    // receiver has read all of it
+    if (tid == 0)
+      for (int r = 1; r < p.mc_world; r++)
+        if (r != p.mc_rank) sg_wait_sys_reached(p.mc_flags_local + kSgMcDoneBase + r, p.mc_epoch - 1);
+    __syncthreads();
+  }
   if (p.chain_local != nullptr) {
     // our call epoch; nothing of the previous call may be overwritten before the next rank has read it
     if (tid == 0) {
@@ -110,7 +132,8 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
       __syncthreads();
     }
     const int r0 = pnl * kSgPullPanelK;
-    const int rows = min(kSgPullPanelK, p.K - r0);
+    const int panel_rows = min(kSgPullPanelK, p.K - r0);
+    const int rows = (panel_rows - ro + nr - 1) / nr;   // the rows of this panel that are ours
     const long long total = (long long)rows * n4;  // < 2^31 (checked on the host)
     for (long long e0 = c * SG_THREADS + tid; e0 < total; e0 += (long long)kSgPullInFlight * stride) {
       float4 v[kSgPullInFlight];
@@ -118,7 +141,7 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
       for (int u = 0; u < kSgPullInFlight; u++) {
         const long long e = e0 + (long long)u * stride;
         if (e < total) {
-          const int row = (int)e / n4, col4 = (int)e - row * n4;
+          const int j = (int)e / n4, col4 = (int)e - j * n4, row = ro + nr * j;
           const float *sp = src + (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4;
           // A coherent load: in a chain the upstream GPU is still writing other panels of this buffer
           // while we read, so the non-coherent (.nc) path, which assumes memory that is read-only for
@@ -131,16 +154,26 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
       for (int u = 0; u < kSgPullInFlight; u++) {
         const long long e = e0 + (long long)u * stride;
         if (e < total) {
-          const int row = (int)e / n4, col4 = (int)e - row * n4;
-          *reinterpret_cast<float4 *>(dst + (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4) = v[u];
+          const int j = (int)e / n4, col4 = (int)e - j * n4, row = ro + nr * j;
+          float *dp = dst + (size_t)(r0 + row) * p.ldb + (size_t)col4 * 4;
+          if (p.mc_mode == 2)   // a multicast address is written with multimem.st: the switch replicates the store
+            asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dp), "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w) : "memory");
+          else
+            *reinterpret_cast<float4 *>(dp) = v[u];
         }
       }
     }
-    __threadfence();
+    if (p.mc_mode == 2) __threadfence_system(); else __threadfence();
     __syncthreads();
     if (tid == 0) {
       unsigned int old;
       asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p.pull_ready + pnl) : "memory");
+      if (p.mc_mode == 2 && old + 1 == p.ready_target) {
+        // last copier of the panel: one multicast store tells every rank that this rank's share has landed
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        asm volatile("multimem.st.release.sys.global.u32 [%0], %1;"
+                     ::"l"(p.mc_flags_mc + (p.mc_rank - 1) * kSgMcMaxGroups + pnl), "r"(p.mc_epoch) : "memory");
+      }
       if (p.chain_local != nullptr && old + 1 == p.ready_target) {
         // last copier of the panel: tell the rank that pulls from us, and count the panel
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_local + pnl), "r"(epoch) : "memory");
@@ -261,6 +294,11 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
   auto need_panel = [&](int k0) {
     const int q = k0 / kSgPullPanelK;
     if (q < panels_known) return;
+    if (p.mc_mode == 2) {   // every receiving rank's share of the panel has landed in our copy
+      for (int o = 0; o < p.mc_world - 1; o++) sg_wait_sys_reached(p.mc_flags_local + o * kSgMcMaxGroups + q, p.mc_epoch);
+      panels_known = q + 1;
+      return;
+    }
     const unsigned long long t0 = sg_timer_ns();
     while ((int)(sg_ld_acquire(p.pull_ready + q) - p.ready_target) < 0)
       if (sg_timer_ns() - t0 > 20000000000ull) __trap();
@@ -385,6 +423,18 @@ __global__ void __launch_bounds__(SG_THREADS, 2) sgemm_kernel(const SgemmArgs p)
       }
     }
   }
+  if constexpr (PULL) {
+    if (p.mc_mode == 2) {
+      // this CTA has read all it needs of B; the last CTA of the launch tells the other receivers so
+      __syncthreads();
+      if (tid == 0) {
+        unsigned int old;
+        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p.mc_done_ctr) : "memory");
+        if (old + 1 == p.mc_done_target)
+          asm volatile("multimem.st.release.sys.global.u32 [%0], %1;" ::"l"(p.mc_flags_mc + kSgMcDoneBase + p.mc_rank), "r"(p.mc_epoch) : "memory");
+      }
+    }
+  }
 }
 
 // Split count for a problem of `tiles` output tiles and depth K on a GPU with room for `room` CTAs.
@@ -495,6 +545,7 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
                                int lda, const float *b_root, float *b_local, int ldb, float beta, float *C,
                                int ldc, int is_root) {
   if (is_root) return cuxb_sgemm_f32(ctx, stream, M, N, K, alpha, A, lda, b_root, ldb, beta, C, ldc);
+  const int mc = (ctx != nullptr && ctx->mc_flags_local != nullptr) ? 2 : 0;   // multicast all-gather, receiving rank
   int rc = ensure_device(ctx);
   if (rc) return rc;
   CUXB_REQUIRE(M >= 0 && N >= 0 && K >= 0, CUXB_ERR_INVALID, "cuxb_mg_sgemm_f32: negative dimension");
@@ -546,6 +597,20 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
   if (ctx->chain_local != nullptr) {
     ctx->sg_pull_done_total += (unsigned int)p.panels;
     p.done_target = ctx->sg_pull_done_total;
+  }
+  p.mc_mode = mc, p.mc_epoch = 0, p.Bdst = nullptr, p.mc_flags_local = nullptr, p.mc_flags_mc = nullptr;
+  p.mc_world = 0, p.mc_rank = 0, p.mc_done_ctr = nullptr, p.mc_done_target = 0;
+  if (mc != 0) {
+    CUXB_REQUIRE(ctx->mc_b != nullptr && p.panels <= kSgMcMaxGroups, CUXB_ERR_INVALID,
+                 "cuxb_mg_sgemm_f32: multicast mode needs the multicast address of the copies of B, and K <= 65536");
+    p.chain_local = nullptr, p.chain_up = nullptr, p.chain_down = nullptr;   // the chain is ignored in multicast mode
+    p.mc_epoch = ++ctx->mc_tab[ctx->mc_cur].calls;
+    p.mc_flags_local = ctx->mc_flags_local, p.mc_flags_mc = ctx->mc_flags_mc;
+    p.mc_world = ctx->mc_world, p.mc_rank = ctx->mc_rank;
+    p.Bdst = (float *)ctx->mc_b;            // the multicast address of every rank's copy
+    p.mc_done_ctr = ctx->sg_pull + 4100;    // local: CTAs finished (never reset)
+    ctx->sg_mc_done_total += grid - (unsigned int)p.n_copy;   // the multiplying CTAs report
+    p.mc_done_target = ctx->sg_mc_done_total;
   }
   sgemm_kernel<true, false, true><<<grid, SG_THREADS, 0, st>>>(p);
   CUXB_LAUNCHED();

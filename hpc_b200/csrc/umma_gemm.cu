@@ -63,7 +63,26 @@ struct UmmaArgs {
   const unsigned int *chain_down;   // the rank that pulls from us (null: nobody)
   unsigned int *done_ctr;           // local: panels published, grows by tiles_n per call
   unsigned int done_target;
+  // NVSwitch multicast all-gather (cuxb_mg_set_multicast), world >= 3.  The root copies nothing.  Each of
+  // the other ranks owns every (world-1)-th 16 KiB box of B: its broadcast warps pull THOSE boxes from
+  // the root (so the root's NVLink egress carries B once, spread over all receivers) and store them to
+  // the multicast address of the ranks' copies -- the switch replicates each store into every rank's
+  // copy, the sender's own included.  Every panel is therefore filled by all receivers at once, at the
+  // full ingress rate of a GPU, and nobody waits for a neighbour to finish first.  Rank r announces
+  // "my share of panel group g of call e has landed everywhere" by a multicast store of e into flag word
+  // (r-1)*kMcMaxGroups + g; a TMA producer waits until the world-1 words of its panel's group carry e.
+  // mc_mode: 0 off, 1 root (multiplies with its own B, takes no part), 2 receiver.
+  int mc_mode;
+  unsigned int mc_epoch;            // this call's number on these flags (host-counted, same on every rank)
+  unsigned int *mc_flags_local;     // this rank's instance of the flags
+  unsigned int *mc_flags_mc;        // the multicast address of the flags
+  int mc_world, mc_rank;
+  int mc_group;                     // panels per announcement (flag word g covers panels [g*mc_group, (g+1)*mc_group))
+  unsigned int *mc_done_ctr;        // local: CTAs that have finished, grows by the grid size per call
+  unsigned int mc_done_target;
 };
+constexpr int kMcMaxGroups = 512;   // flag words per sending rank
+constexpr int kMcDoneBase = 4100;    // flag word kMcDoneBase + r: last call whose B rank r has read completely
 constexpr int kChainDone = 4096;
 
 template <int CG>
@@ -230,7 +249,13 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           const unsigned long long t0 = global_timer_ns_();
           while ((long long)ld_acquire_gpu_u32(p.wave_sync) < target && global_timer_ns_() - t0 < 4000ull) {}
         }
-        if (p.b_ready != nullptr) {
+        if (p.mc_mode == 2) {
+          // multicast all-gather: this panel is complete here once every receiving rank (ourselves
+          // included) has announced its share of the panel's group for this call
+          for (int o = 0; o < p.mc_world - 1; o++)
+            wait_sys_reached(p.mc_flags_local + o * kMcMaxGroups + tn / p.mc_group, p.mc_epoch);
+          asm volatile("fence.proxy.async;" ::: "memory");
+        } else if (p.b_ready != nullptr && p.mc_mode == 0) {
           // this column panel of B is being pulled from the root GPU: wait until every copy warp has
           // delivered its share, then order the TMA (async-proxy) reads behind that observation
           const unsigned long long t0 = global_timer_ns_();
@@ -307,11 +332,16 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       constexpr int kRowBoxes = UG_BLOCK_N / kPullRows;          // K-major only: row chunks per panel
       const int boxes_per_panel = B_MN ? (p.K + kPullRows - 1) / kPullRows : ((p.K + 255) / 256) * kRowBoxes;
       const int G = gridDim.x, me = blockIdx.x;
-      const int mine_per_panel = (boxes_per_panel - me + G - 1) / G;  // boxes c = me, me+G, ... < boxes_per_panel
+      // Which boxes of a panel are ours?  Pull / chain: every box, so box c belongs to CTA (c mod grid).
+      // Multicast all-gather: this RANK owns boxes c = ro + nr * j (ro = rank - 1, nr = world - 1), and of
+      // those, j = me, me + G, ... belong to this CTA.
+      const int nr = p.mc_mode == 2 ? p.mc_world - 1 : 1, ro = p.mc_mode == 2 ? p.mc_rank - 1 : 0;
+      const int rank_boxes = (boxes_per_panel - ro + nr - 1) / nr;
+      const int mine_per_panel = (rank_boxes - me + G - 1) / G;
       const long long total = (long long)mine_per_panel * p.tiles_n;
       auto coords = [&](long long i, int &panel, int &x, int &y) {
         panel = (int)(i / mine_per_panel);
-        const int c = me + (int)(i % mine_per_panel) * G;
+        const int c = ro + nr * (me + (int)(i % mine_per_panel) * G);
         if (B_MN) x = panel * UG_BLOCK_N, y = c * kPullRows;
         else x = (c / kRowBoxes) * 256, y = panel * UG_BLOCK_N + (c % kRowBoxes) * kPullRows;
       };
@@ -321,6 +351,12 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       if (p.chain_local != nullptr) {
         epoch = ld_acquire_sys_u32(p.chain_local + kChainDone) + 1;
         if (p.chain_down != nullptr) wait_sys_reached(p.chain_down + kChainDone, epoch - 1);
+      }
+      if (p.mc_mode == 2) {
+        // our stores land in EVERY rank's copy: nothing of the previous call may be overwritten before
+        // every receiver has read all of it (we ourselves have: calls of one context run in stream order)
+        for (int r = 1; r < p.mc_world; r++)
+          if (r != p.mc_rank) wait_sys_reached(p.mc_flags_local + kMcDoneBase + r, p.mc_epoch - 1);
       }
       int up_known = 0;  // panels of the upstream copy known to be complete
       // The upstream flag lives on another GPU: a look at it is an NVLink round trip.  The copy loop
@@ -357,6 +393,18 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         pend_panel = -1;
       };
       auto arrive = [&](int panel) {
+        if (p.mc_mode == 2) {
+          // our stores of this group are complete (wait_group 0 above); order them, system-wide, before
+          // the count -- whoever completes the count announces this rank's share to every rank at once
+          const int grp = panel / p.mc_group;   // `panel` is the last panel of its group
+          asm volatile("fence.acq_rel.sys;" ::: "memory");
+          if (atom_add_acq_rel_gpu(p.b_ready + grp, 1u) + 1 == p.ready_target) {
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+            asm volatile("multimem.st.release.sys.global.u32 [%0], %1;"
+                         ::"l"(p.mc_flags_mc + (p.mc_rank - 1) * kMcMaxGroups + grp), "r"(p.mc_epoch) : "memory");
+          }
+          return;
+        }
         if (p.chain_local == nullptr) {
           asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.b_ready + panel) : "memory");
           return;
@@ -365,6 +413,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         pend_old = atom_add_acq_rel_gpu(p.b_ready + panel, 1u);
         pend_panel = panel;
       };
+      int pend_arrive = -1;   // panel whose last store is committed but not yet confirmed
       if (total > 0) issue(0);
       if (total > 1) issue(1);
       for (long long i = 0; i < total; i++) {
@@ -377,21 +426,38 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                      ::"l"(&map_bdst), "r"(buf), "r"(x), "r"(y) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        const bool last_of_panel = ((i + 1) % mine_per_panel) == 0;
-        if (last_of_panel) {
-          asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // every store of this panel is complete
+        // The store that completed a panel one box ago has had a whole box time to land: confirm it now
+        // (all but the newest bulk group complete) and announce the panel.  Waiting for it right after its
+        // commit instead would leave this thread idle for a full store round trip once per panel -- with
+        // 3-4 boxes per panel and CTA that cost a quarter of the copy rate.
+        if (pend_arrive >= 0) {
+          asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
           asm volatile("fence.proxy.async;" ::: "memory");
           __threadfence();
-          arrive(panel);
+          arrive(pend_arrive);
+          pend_arrive = -1;
         }
+        // When does this CTA tell the others that its share has landed?  Pull: after every panel.  Multicast
+        // all-gather: after every mc_group panels (each announcement is a multicast round trip).
+        bool last_of_panel = ((i + 1) % mine_per_panel) == 0;
+        if (p.mc_mode == 2 && last_of_panel)
+          last_of_panel = ((panel + 1) % p.mc_group) == 0 || panel + 1 == p.tiles_n;
+        if (last_of_panel) pend_arrive = panel;
         if (i + 2 < total) {
-          if (!last_of_panel) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging buffer free again
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging buffer free again
           issue(i + 2);
         }
       }
+      if (pend_arrive >= 0) {
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // every store is complete
+        asm volatile("fence.proxy.async;" ::: "memory");
+        __threadfence();
+        arrive(pend_arrive);
+      }
       // CTAs that own no box of a panel still have to be counted
       if (mine_per_panel == 0)
-        for (int panel = 0; panel < p.tiles_n; panel++) arrive(panel);
+        for (int panel = 0; panel < p.tiles_n; panel++)
+          if (p.mc_mode != 2 || (panel + 1) % p.mc_group == 0 || panel + 1 == p.tiles_n) arrive(panel);
       settle();
     }
     __syncwarp();
@@ -441,6 +507,12 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   tc_fence_before();
   if (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 2) tmem_dealloc<CG>(tmem_base, kTmemCols);
+  if (p.mc_mode == 2 && threadIdx.x == 0) {
+    // every tile of this CTA has been multiplied, so all of its loads of B are done.  The last CTA of
+    // the launch tells the other receivers that this rank is finished with the call's B (they may then overwrite it).
+    if (atom_add_acq_rel_gpu(p.mc_done_ctr, 1u) + 1 == p.mc_done_target)
+      asm volatile("multimem.st.release.sys.global.u32 [%0], %1;" ::"l"(p.mc_flags_mc + kMcDoneBase + p.mc_rank), "r"(p.mc_epoch) : "memory");
+  }
 }
 
 // ------------------------------------------------------------------------------- host side
@@ -503,7 +575,8 @@ static int make_map(cuxb_ctx *ctx, CUtensorMap *map, const void *base, int ebyte
 
 template <int KIND, bool B_MN, int CT, int CG>
 static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, float alpha, const void *A, int lda,
-                       const void *B, int ldb, float beta, void *C, int ldc, const void *b_pull_from = nullptr) {
+                       const void *B, int ldb, float beta, void *C, int ldc, const void *b_pull_from = nullptr,
+                       int mc_role = 0) {
   typedef UmmaCfg<CG> Cfg;
   constexpr int ebytes = (KIND == KIND_S8) ? 1 : 2;
   constexpr int kBlockK = UG_ROW_BYTES / ebytes;
@@ -532,8 +605,48 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   int clusters = ctx->sm_count / CG;
   if (clusters > total) clusters = total;
 
+  p.mc_mode = 0, p.mc_epoch = 0, p.mc_flags_local = nullptr, p.mc_flags_mc = nullptr;
+  p.mc_world = 0, p.mc_rank = 0, p.mc_group = 1, p.mc_done_ctr = nullptr, p.mc_done_target = 0;
   CUtensorMap msrc = mb, mdst = mb;  // unused unless B is pulled from another GPU
-  if (b_pull_from != nullptr) {
+  if (mc_role == 2) {
+    // NVSwitch multicast all-gather, receiving rank: B = this rank's copy (what the GEMM reads),
+    // b_pull_from = the root's B as mapped here (what our share is pulled from), ctx->mc_b = the multicast
+    // address of the ranks' copies (where our share is stored to).
+    CUXB_REQUIRE(p.tiles_n <= 4096, CUXB_ERR_TOO_LARGE, "fused B broadcast: N too large");
+    CUXB_REQUIRE(b_pull_from != nullptr && ctx->mc_b != nullptr, CUXB_ERR_INVALID,
+                 "multicast broadcast: the root's B or the multicast address of the copies is missing");
+    if (ctx->bcast_ready == nullptr) {
+      CUXB_CUDA(cudaMalloc((void **)&ctx->bcast_ready, (4096 + 32) * sizeof(unsigned int)));
+      CUXB_CUDA(cudaMemset(ctx->bcast_ready, 0, (4096 + 32) * sizeof(unsigned int)));
+      ctx->bcast_done_total = 0, ctx->bcast_calls = 0, ctx->bcast_grid = 0, ctx->bcast_panels = 0;
+    }
+    p.mc_mode = 2;
+    p.mc_epoch = ++ctx->mc_tab[ctx->mc_cur].calls;
+    p.mc_flags_local = ctx->mc_flags_local, p.mc_flags_mc = ctx->mc_flags_mc;
+    p.mc_world = ctx->mc_world, p.mc_rank = ctx->mc_rank;
+    // about eight announcements per call (the first wave of tiles needs ~ten panels before it can start
+    // anyway; every announcement drains the announcing thread's stores through the switch)
+    p.mc_group = p.tiles_n / 8 < 1 ? 1 : (p.tiles_n / 8 > 8 ? 8 : p.tiles_n / 8);
+    if (ctx->dbg_mc_group > 0) p.mc_group = ctx->dbg_mc_group;
+    while ((p.tiles_n + p.mc_group - 1) / p.mc_group > kMcMaxGroups) p.mc_group *= 2;
+    const uint64_t rows = B_MN ? (uint64_t)K : (uint64_t)N, cols = B_MN ? (uint64_t)N : (uint64_t)K;
+    const uint32_t box_rows = (KIND == KIND_S8) ? 64 : 32;
+    rc = make_map(ctx, &msrc, b_pull_from, ebytes, dt, rows, cols, (uint64_t)ldb, 256, box_rows, false);
+    if (rc) return rc;
+    rc = make_map(ctx, &mdst, ctx->mc_b, ebytes, dt, rows, cols, (uint64_t)ldb, 256, box_rows, false);
+    if (rc) return rc;
+    // (a different announcement group changes which counters a call touches: encoded into the panel count)
+    if (ctx->bcast_grid != clusters * CG || ctx->bcast_panels != p.tiles_n + 65536 * p.mc_group) {
+      CUXB_CUDA(cudaMemsetAsync(ctx->bcast_ready, 0, 4096 * sizeof(unsigned int), st));
+      ctx->bcast_calls = 0, ctx->bcast_grid = clusters * CG, ctx->bcast_panels = p.tiles_n + 65536 * p.mc_group;
+    }
+    ctx->bcast_calls++;
+    p.b_ready = ctx->bcast_ready;
+    p.ready_target = ctx->bcast_calls * (unsigned int)(clusters * CG);
+    p.mc_done_ctr = ctx->bcast_ready + 4096 + 8;  // beyond the panel counters, never reset
+    ctx->mc_done_total += (unsigned int)(clusters * CG);
+    p.mc_done_target = ctx->mc_done_total;
+  } else if (b_pull_from != nullptr) {
     CUXB_REQUIRE(p.tiles_n <= 4096, CUXB_ERR_TOO_LARGE, "fused B broadcast: N too large");
     // un-swizzled copy boxes (see the broadcast warp): 256 elements wide, 32 rows (64 for int8) = 16 KiB
     const uint64_t rows = B_MN ? (uint64_t)K : (uint64_t)N, cols = B_MN ? (uint64_t)N : (uint64_t)K;
@@ -630,6 +743,12 @@ static int check_common(const char *name, cuxb_ctx *ctx, int M, int N, int K, co
   return 0;
 }
 
+// multicast all-gather role of a cuxb_mg_* call on this context: 0 = off (or the root, which takes no
+// part: it multiplies with its own B), 2 = receiving rank
+static int mc_role_of(const cuxb_ctx *ctx, int is_root) {
+  return (ctx != nullptr && ctx->mc_flags_local != nullptr && !is_root) ? 2 : 0;
+}
+
 const void *umma_kernel_symbol() { return (const void *)umma_gemm_kernel<KIND_F16, true, CUXB_FLOAT16, 2>; }
 int umma_smem_bytes() { return UmmaCfg<2>::kSmemBytes; }
 
@@ -642,11 +761,13 @@ using namespace cuxb;
 //   what 0: MMA variant, value 0 = default (CTA pair), 1 = single CTA, 2 = CTA pair
 //   what 1: rasterisation group height (tile rows per L2 group), 0 = default, 1..64
 //   what 2: soft per-wave rendezvous of the TMA producers, value 1 = on (default), 0 = off
+//   what 3: multicast broadcast, panels per announcement, 0 = default (about eight announcements per call)
 CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (ctx == nullptr) return CUXB_ERR_INVALID;
   if (what == 0 && value >= 0 && value <= 2) return ctx->dbg_cta_group = value, 0;
   if (what == 1 && value >= 0 && value <= 64) return ctx->dbg_group_m = value, 0;
   if (what == 2) return ctx->dbg_no_wave_sync = value ? 0 : 1, 0;
+  if (what == 3 && value >= 0 && value <= 64) return ctx->dbg_mc_group = value, 0;
   return CUXB_ERR_INVALID;
 }
 
@@ -731,10 +852,11 @@ CUXB_API int cuxb_mg_hgemm_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N,
                "cuxb_mg_hgemm_f16_f32acc: b_root is null or not 16-byte aligned");
   CUXB_REQUIRE(lda >= K && ldb >= N && ldc >= N, CUXB_ERR_INVALID, "cuxb_mg_hgemm_f16_f32acc: leading dimension too small");
   cudaStream_t st = (cudaStream_t)stream;
+  const int mc = mc_role_of(ctx, is_root);
   const void *pull = is_root ? nullptr : b_root;
   if (c_dtype == CUXB_FLOAT16)
-    return launch_umma<KIND_F16, true, CUXB_FLOAT16, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, pull);
-  return launch_umma<KIND_F16, true, CUXB_FLOAT32, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, pull);
+    return launch_umma<KIND_F16, true, CUXB_FLOAT16, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, pull, mc);
+  return launch_umma<KIND_F16, true, CUXB_FLOAT32, 2>(ctx, st, M, N, K, alpha, A, lda, B, ldb, beta, C, ldc, pull, mc);
 }
 
 // Row-sharded int8 linear with the broadcast of Bt fused into the kernel (the same decomposition, for
@@ -747,9 +869,10 @@ CUXB_API int cuxb_mg_linear_s8_s32(cuxb_ctx *ctx, void *stream, int M, int N, in
   if (rc) return rc < 0 ? 0 : rc;
   CUXB_REQUIRE(bt_root != nullptr && ((uintptr_t)bt_root & 15) == 0, CUXB_ERR_INVALID,
                "cuxb_mg_linear_s8_s32: bt_root is null or not 16-byte aligned");
+  const int mc = mc_role_of(ctx, is_root);
   const void *pull = is_root ? nullptr : (const void *)bt_root;
   return launch_umma<KIND_S8, false, CUXB_INT32, 2>(ctx, (cudaStream_t)stream, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N,
-                                                    pull);
+                                                    pull, mc);
 }
 
 // The same for the 16-bit linears (linear.cpp:137-182's layout): Bt[N,K] pulled in 256-k x 32-row boxes.
@@ -762,11 +885,12 @@ CUXB_API int cuxb_mg_linear_bf16_f32acc(cuxb_ctx *ctx, void *stream, int M, int 
   if (rc) return rc < 0 ? 0 : rc;
   CUXB_REQUIRE(bt_root != nullptr && ((uintptr_t)bt_root & 15) == 0, CUXB_ERR_INVALID,
                "cuxb_mg_linear_bf16_f32acc: bt_root is null or not 16-byte aligned");
+  const int mc = mc_role_of(ctx, is_root);
   const void *pull = is_root ? nullptr : bt_root;
   cudaStream_t st = (cudaStream_t)stream;
   if (c_dtype == CUXB_BFLOAT16)
-    return launch_umma<KIND_BF16, false, CUXB_BFLOAT16, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
-  return launch_umma<KIND_BF16, false, CUXB_FLOAT32, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
+    return launch_umma<KIND_BF16, false, CUXB_BFLOAT16, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull, mc);
+  return launch_umma<KIND_BF16, false, CUXB_FLOAT32, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull, mc);
 }
 CUXB_API int cuxb_mg_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, const void *A,
                                        const void *bt_root, void *bt_local, void *C, int c_dtype, int is_root) {
@@ -777,9 +901,10 @@ CUXB_API int cuxb_mg_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N
   if (rc) return rc < 0 ? 0 : rc;
   CUXB_REQUIRE(bt_root != nullptr && ((uintptr_t)bt_root & 15) == 0, CUXB_ERR_INVALID,
                "cuxb_mg_linear_f16_f32acc: bt_root is null or not 16-byte aligned");
+  const int mc = mc_role_of(ctx, is_root);
   const void *pull = is_root ? nullptr : bt_root;
   cudaStream_t st = (cudaStream_t)stream;
   if (c_dtype == CUXB_FLOAT16)
-    return launch_umma<KIND_F16, false, CUXB_FLOAT16, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
-  return launch_umma<KIND_F16, false, CUXB_FLOAT32, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull);
+    return launch_umma<KIND_F16, false, CUXB_FLOAT16, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull, mc);
+  return launch_umma<KIND_F16, false, CUXB_FLOAT32, 2>(ctx, st, M, N, K, 1.f, A, K, Bt, K, 0.f, C, N, pull, mc);
 }

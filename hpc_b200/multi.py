@@ -126,15 +126,39 @@ class PeerExchange:
         R.b_local = R.ptrs[r]
         src, up, down = chain_plan(w, r, mode)
         R.b_up = R.ptrs[src if src is not None else 0]
+        if mode == "mcast":
+            # scatter from the root + NVSwitch multicast all-gather between the receivers (3+ ranks)
+            if w < 3:
+                raise RuntimeError("multicast all-gather needs 3+ ranks (with two, the one receiver pulls from the root)")
+            mc = int(getattr(R.handle, "multicast_ptr", 0) or 0)
+            F = self.symmetric_like(torch.empty(capi.MG_MCAST_FLAGS_BYTES // 4, dtype=torch.int32, device=B.device))
+            fmc = int(getattr(F.handle, "multicast_ptr", 0) or 0)
+            if not mc or not fmc:
+                raise RuntimeError("no NVSwitch multicast mapping available for symmetric memory on this box")
+            F.tensor.zero_()
+            R.flags = F
+            R.b_up = R.ptrs[0]          # every receiver pulls its share straight from the root's B
+            if r == 0:
+                R.activate = lambda: (ctx.mg_set_chain(0, 0, 0), ctx.mg_set_multicast(0, 0, 0, 0, 0))
+            else:
+                R.activate = lambda: (ctx.mg_set_chain(0, 0, 0), ctx.mg_set_multicast(w, r, F.ptrs[r], fmc, mc))
+            R.describe = ("every receiver pulls 1/%d of B from the root and stores it to an NVSwitch multicast address "
+                          "(scatter + multicast all-gather: the root sends B once, no hops)" % (w - 1))
+            R.clear_local = (lambda: R.tensor.zero_()) if r > 0 else (lambda: None)
+            R.local_equals = lambda Bt: bool(torch.equal(R.tensor, Bt))
+            torch.cuda.synchronize()
+            dist.barrier()
+            return R
         if mode == "chain" and w > 2:
             F = self.symmetric_like(torch.empty(capi.MG_CHAIN_FLAGS_BYTES // 4, dtype=torch.int32, device=B.device))
             F.tensor.zero_()
             R.flags = F
             chain = (F.ptrs[r], F.ptrs[up] if up is not None else 0, F.ptrs[down] if down is not None else 0)
-            R.activate = (lambda: ctx.mg_set_chain(*chain)) if r > 0 else (lambda: None)
+            R.activate = (lambda: (ctx.mg_set_multicast(0, 0, 0, 0, 0), ctx.mg_set_chain(*chain))) if r > 0 else \
+                (lambda: ctx.mg_set_multicast(0, 0, 0, 0, 0))
             R.describe = "from the rank before it (chain: each GPU sends B once)"
         else:
-            R.activate = lambda: ctx.mg_set_chain(0, 0, 0)
+            R.activate = lambda: (ctx.mg_set_multicast(0, 0, 0, 0, 0), ctx.mg_set_chain(0, 0, 0))
             R.describe = "straight from rank 0 (star)"
         R.clear_local = (lambda: R.tensor.zero_()) if r > 0 else (lambda: None)
         R.local_equals = lambda Bt: bool(torch.equal(R.tensor, Bt))

@@ -213,6 +213,31 @@ int cuxb_mg_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, 
  * switches back to pulling from the root. */
 #define CUXB_MG_CHAIN_FLAGS_BYTES 16640
 int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *flags_up, const void *flags_down);
+/* NVSwitch multicast all-gather (3..8 ranks on a box whose GPUs sit behind an NVSwitch).  The chain above
+ * needs world - 1 hops before the last rank sees the first panel, and every hop moves all of B.  Here the
+ * root copies nothing and every other rank owns every (world-1)-th 16 KiB box of B (SGEMM: every
+ * (world-1)-th row): its kernel pulls THOSE boxes from the root -- so the root's NVLink egress carries B
+ * once, spread over all receivers -- and stores them to a MULTICAST address, which the switch replicates
+ * into every rank's copy of B.  Every panel is filled by all receivers at once at the full ingress rate of
+ * a GPU; each rank announces its share of a panel group with one multicast store into the flags, and a
+ * rank starts loading a panel once all world - 1 announcements for it are in its own instance of the flags.
+ * After this call, for the cuxb_mg_*gemm / cuxb_mg_linear_* calls of this context (non-root ranks; the root
+ * needs no call -- it multiplies with its own B as before):
+ *   b_root / bt_root   = the root's B as mapped into this process (what this rank's share is pulled from)
+ *   b_local / bt_local = this rank's copy (what its GEMM reads)
+ *   b_mc               = the multicast address of the ranks' copies (a multicast object bound to one
+ *                        allocation per GPU: cuMulticastCreate / cuMulticastBindMem, torch symmetric memory's
+ *                        multicast_ptr, or cuxb_mg_create's buffers); the copies must have b_local's layout
+ *   flags_local        = this rank's instance of the flags (CUXB_MG_MCAST_FLAGS_BYTES, zeroed once before
+ *                        the first call); flags_mc = the multicast address of the flags
+ * A rank does not overwrite the copies before every receiver has reported (through the flags) that it has
+ * read all of the previous call's B.  Every non-root rank must make the same sequence of calls.  The root
+ * must leave B untouched until every rank's call has finished.  flags_local == NULL switches the mode off.
+ * Host-side state only; a chain set with cuxb_mg_set_chain is ignored while this mode is on.  Has no
+ * counterpart in the reference; the transfer it replaces is the MPI_Send of B to every worker,
+ * mpi/alg_matrix_multiply.cpp:57-62. */
+#define CUXB_MG_MCAST_FLAGS_BYTES 16640
+int cuxb_mg_set_multicast(cuxb_ctx *ctx, int world, int rank, void *flags_local, void *flags_mc, void *b_mc);
 int cuxb_enable_peer_access(int device, int peer_device);
 
 /* ---- GEMM: C = alpha * A[M,K] * B[K,N] + beta * C, row-major.
