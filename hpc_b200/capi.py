@@ -74,6 +74,23 @@ SIGNATURES = {
     "cuxb_mg_set_chain": ([_vp, _vp, _vp, _vp], _i),
     "cuxb_mg_set_multicast": ([_vp, _i, _i, _vp, _vp, _vp], _i),
     "cuxb_enable_peer_access": ([_i, _i], _i),
+    "cuxb_mg_create": ([_i, C.POINTER(_i), C.POINTER(_vp)], _i),
+    "cuxb_mg_destroy": ([_vp], _i),
+    "cuxb_mg_world": ([_vp], _i),
+    "cuxb_mg_device": ([_vp, _i], _i),
+    "cuxb_mg_ctx": ([_vp, _i], _vp),
+    "cuxb_mg_stream": ([_vp, _i], _vp),
+    "cuxb_mg_sync": ([_vp], _i),
+    "cuxb_mg_all_dot_f32": ([_vp, C.POINTER(_ll), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp)], _i),
+    "cuxb_mg_all_sum_f32": ([_vp, C.POINTER(_ll), C.POINTER(_vp), C.POINTER(_vp)], _i),
+    "cuxb_mg_all_nrm2_f32": ([_vp, C.POINTER(_ll), C.POINTER(_vp), C.POINTER(_vp)], _i),
+    "cuxb_mg_all_scan_i32": ([_vp, C.POINTER(_ll), C.POINTER(_vp), C.POINTER(_vp)], _i),
+    "cuxb_mg_all_sgemm_f32": ([_vp, C.POINTER(_i), _i, _i, _f, C.POINTER(_vp), _i, _vp, _i, _f, C.POINTER(_vp), _i], _i),
+    "cuxb_mg_all_hgemm_f16_f32acc": ([_vp, C.POINTER(_i), _i, _i, _f, C.POINTER(_vp), _i, _vp, _i, _f, C.POINTER(_vp), _i, _i], _i),
+    "cuxb_mg_all_linear_s8_s32": ([_vp, C.POINTER(_i), _i, _i, C.POINTER(_vp), _vp, C.POINTER(_vp)], _i),
+    "cuxb_ipc_export": ([_vp, _vp], _i),
+    "cuxb_ipc_import": ([_vp, C.POINTER(_vp)], _i),
+    "cuxb_ipc_close": ([_vp], _i),
     "cuxb_sgemm_f32": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i], _i),
     "cuxb_hgemm_f16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
     "cuxb_gemm_bf16_f32acc": ([_vp, _vp, _i, _i, _i, _f, _vp, _i, _vp, _i, _f, _vp, _i, _i], _i),
@@ -305,3 +322,86 @@ class Context:
 
 def launch_count():
     return lib().cuxb_launch_count()
+
+
+class MultiGpu:
+    """cuxb_mg wrapper: one host thread driving `devices` (see include/cuxb.h).  Arguments of the all_* calls
+    are lists indexed by rank: element counts / row counts and device pointers (ints) on that rank's GPU."""
+
+    def __init__(self, devices):
+        devices = list(devices)
+        self._h = _vp()
+        arr = (_i * len(devices))(*devices)
+        check(lib().cuxb_mg_create(len(devices), arr, C.byref(self._h)), "cuxb_mg_create")
+        self.world = len(devices)
+        self.devices = devices
+
+    def close(self):
+        if self._h:
+            lib().cuxb_mg_destroy(self._h)
+            self._h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stream(self, rank):
+        return lib().cuxb_mg_stream(self._h, rank)
+
+    def sync(self):
+        check(lib().cuxb_mg_sync(self._h), "cuxb_mg_sync")
+
+    def _ptrs(self, ps):
+        assert len(ps) == self.world
+        return (_vp * self.world)(*ps)
+
+    def _lens(self, ns):
+        return (_ll * self.world)(*ns)
+
+    def _rows(self, ms):
+        return (_i * self.world)(*ms)
+
+    def all_dot_f32(self, n, a, b, res):
+        check(lib().cuxb_mg_all_dot_f32(self._h, self._lens(n), self._ptrs(a), self._ptrs(b), self._ptrs(res)), "cuxb_mg_all_dot_f32")
+
+    def all_sum_f32(self, n, x, res):
+        check(lib().cuxb_mg_all_sum_f32(self._h, self._lens(n), self._ptrs(x), self._ptrs(res)), "cuxb_mg_all_sum_f32")
+
+    def all_nrm2_f32(self, n, x, res):
+        check(lib().cuxb_mg_all_nrm2_f32(self._h, self._lens(n), self._ptrs(x), self._ptrs(res)), "cuxb_mg_all_nrm2_f32")
+
+    def all_scan_i32(self, n, src, dst):
+        check(lib().cuxb_mg_all_scan_i32(self._h, self._lens(n), self._ptrs(src), self._ptrs(dst)), "cuxb_mg_all_scan_i32")
+
+    def all_sgemm_f32(self, M, N, K, alpha, A, lda, B_root, ldb, beta, Cp, ldc):
+        check(lib().cuxb_mg_all_sgemm_f32(self._h, self._rows(M), N, K, alpha, self._ptrs(A), lda, B_root, ldb, beta,
+                                          self._ptrs(Cp), ldc), "cuxb_mg_all_sgemm_f32")
+
+    def all_hgemm_f16(self, M, N, K, alpha, A, lda, B_root, ldb, beta, Cp, ldc, c_dtype=FLOAT16):
+        check(lib().cuxb_mg_all_hgemm_f16_f32acc(self._h, self._rows(M), N, K, alpha, self._ptrs(A), lda, B_root, ldb, beta,
+                                                 self._ptrs(Cp), ldc, c_dtype), "cuxb_mg_all_hgemm_f16_f32acc")
+
+    def all_linear_s8(self, M, N, K, A, Bt_root, Cp):
+        check(lib().cuxb_mg_all_linear_s8_s32(self._h, self._rows(M), N, K, self._ptrs(A), Bt_root, self._ptrs(Cp)),
+              "cuxb_mg_all_linear_s8_s32")
+
+
+def ipc_export(dptr):
+    """64-byte handle (bytes) of a cuxb_malloc'ed device buffer, for another process to cuxb_ipc_import."""
+    buf = C.create_string_buffer(64)
+    check(lib().cuxb_ipc_export(dptr, buf), "cuxb_ipc_export")
+    return buf.raw
+
+
+def ipc_import(handle):
+    out = _vp()
+    check(lib().cuxb_ipc_import(C.c_char_p(handle), C.byref(out)), "cuxb_ipc_import")
+    return out.value
+
+
+def dmalloc(nbytes):
+    out = _vp()
+    check(lib().cuxb_malloc(C.byref(out), nbytes), "cuxb_malloc")
+    return out.value

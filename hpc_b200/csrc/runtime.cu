@@ -208,6 +208,28 @@ CUXB_API int cuxb_enable_peer_access(int device, int peer_device) {
   return 0;
 }
 
+// One process per GPU: export / import of device buffers between processes (see cuxb.h).
+CUXB_API int cuxb_ipc_export(void *dptr, void *handle_out) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == CUXB_IPC_HANDLE_BYTES, "handle size");
+  CUXB_REQUIRE(dptr != nullptr && handle_out != nullptr, CUXB_ERR_INVALID, "cuxb_ipc_export: null pointer");
+  cudaIpcMemHandle_t h;
+  CUXB_CUDA(cudaIpcGetMemHandle(&h, dptr));
+  memcpy(handle_out, &h, sizeof(h));
+  return 0;
+}
+CUXB_API int cuxb_ipc_import(const void *handle, void **dptr_out) {
+  CUXB_REQUIRE(handle != nullptr && dptr_out != nullptr, CUXB_ERR_INVALID, "cuxb_ipc_import: null pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, sizeof(h));
+  *dptr_out = nullptr;
+  CUXB_CUDA(cudaIpcOpenMemHandle(dptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+CUXB_API int cuxb_ipc_close(void *dptr) {
+  if (dptr) CUXB_CUDA(cudaIpcCloseMemHandle(dptr));
+  return 0;
+}
+
 // Chained broadcast for the cuxb_mg_*gemm / cuxb_mg_linear_* calls of this context (see cuxb.h).
 CUXB_API int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *flags_up, const void *flags_down) {
   CUXB_REQUIRE(ctx != nullptr, CUXB_ERR_INVALID, "cuxb_mg_set_chain: null context");

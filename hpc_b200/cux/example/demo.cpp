@@ -6,7 +6,7 @@
 // added through the OpFactory.  Unlike the reference it returns a status: non-zero if any check
 // failed, and it also compares host kernel 0 with device kernel 0 (the reference never does).
 //
-//   cux_demo [--len N] [--quick] [--device-fill] [--pinned] [--device-only] [--gemm-block B]
+//   cux_demo [--len N] [--quick] [--device-fill] [--pinned] [--device-only] [--gemm-block B] [--gpus G] [--multi-only]
 //            [--gemm-range LO HI] [--linear M N K] [--scan-len N]
 //   BASELINE sizes through the cux harness:
 //   cux_demo --device-only --device-fill --len 268435456 --gemm-block 512 --gemm-range -1 1
@@ -140,6 +140,62 @@ void ScanTest(int n) {
   Finish(ex, "scan_i32");
 }
 
+// --gpus g: the same operators sharded over g GPUs by cux::MultiExecutor (one host thread, the C ABI's
+// cuxb_mg driver): dot and scan over contiguous slices, gemm over row blocks of A and C with B on rank 0
+// only -- the master / worker flow of mpi/alg_matrix_multiply.cpp:52-80.  The expected values come from the
+// host kernels of the single-device Executor; the verdicts from cux's ResultChecker.
+void MultiGpuTest(int gpus, int data_len, int scan_len) {
+  std::vector<int> devs;
+  for (int d = 0; d < gpus; d++) devs.push_back(d);
+  cux::MultiExecutor mex;
+  mex.InitializeMulti(devs);
+  {  // dot
+    cux::Executor ex;
+    ex.Initialize(0);
+    ex.SelectOp("dot", "");
+    cux::Array4D a(1, 1, 1, data_len), b(1, 1, 1, data_len), out(1, 1, 1, 1);
+    ex.BindAndFill({&a, &b}, {&out}, -2, 2, 0);
+    ex.Run(cux::OpRunMode::ON_HOST);
+    const float expect = out.GetCpuData<float>(cux::NO_PUSH)[0];
+    const bool ok = mex.RunDot(a.GetCpuData<float>(cux::NO_PUSH), b.GetCpuData<float>(cux::NO_PUSH), data_len, expect);
+    std::printf("> multi-GPU dot over %d GPUs, %d elements: %s (%.3f ms incl. launch + sync)\n", gpus, data_len, ok ? "Pass" : "FAIL", mex.last_ms());
+    if (!ok) g_failures++;
+    ex.Clear();
+  }
+  {  // gemm: 128-row tiles per rank, alpha 1 beta 3 as the demo
+    const int M = 256 * gpus, N = 512, K = 384;
+    cux::Executor ex;
+    ex.Initialize(0);
+    ex.SelectOp("gemm", "alpha: 1.0, beta: 3.0");
+    cux::Array4D A(1, 1, M, K), B(1, 1, K, N), C(1, 1, M, N);
+    ex.BindAndFill({&A, &B}, {&C}, -2, 5, 0);
+    const std::vector<float> c0 = Snapshot<float>(&C);
+    ex.Run(cux::OpRunMode::ON_HOST);
+    const std::vector<float> expect = Snapshot<float>(&C);
+    const bool ok = mex.RunGemm(M, N, K, 1.0f, A.GetCpuData<float>(cux::NO_PUSH), B.GetCpuData<float>(cux::NO_PUSH), 3.0f,
+                                c0.data(), expect.data());
+    std::printf("> multi-GPU gemm fp32 %dx%dx%d over %d GPUs (rows sharded, B fetched from rank 0 inside the kernel): %s (%.3f ms)\n",
+                M, N, K, gpus, ok ? "Pass" : "FAIL", mex.last_ms());
+    if (!ok) g_failures++;
+    ex.Clear();
+  }
+  {  // scan
+    cux::Executor ex;
+    ex.Initialize(0);
+    ex.SelectOp("scan_i32", "");
+    cux::Array4D in(1, 1, 1, scan_len), out(1, 1, 1, scan_len);
+    ex.BindAndFill({&in}, {&out}, -2, 2, 0);
+    ex.Run(cux::OpRunMode::ON_HOST);
+    const std::vector<int32_t> expect = Snapshot<int32_t>(&out);
+    const bool ok = mex.RunScanI32(in.GetCpuData<int32_t>(cux::NO_PUSH), scan_len, expect.data());
+    std::printf("> multi-GPU scan_i32 over %d GPUs, %d elements: %s (%.3f ms)\n", gpus, scan_len, ok ? "Pass" : "FAIL", mex.last_ms());
+    if (!ok) g_failures++;
+    ex.Clear();
+  }
+  if (!mex.AllChecksPassed()) g_failures++;
+  mex.Clear();
+}
+
 }  // namespace
 
 int main(int argc, char **argv) {
@@ -148,6 +204,8 @@ int main(int argc, char **argv) {
   int lin_m = 200, lin_n = 304, lin_k = 400;  // simd/x86/linear.cpp:254 (N rounded up to a multiple of 4)
   int scan_len = -1;
   int gemm_lo = -2, gemm_hi = 5;  // demo.cpp:97
+  int gpus = 0;                   // --gpus g: also run dot / gemm / scan sharded over g GPUs
+  bool multi_only = false;        // --multi-only: skip the single-GPU tests
   for (int i = 1; i < argc; i++) {
     if (!std::strcmp(argv[i], "--len") && i + 1 < argc) data_len = std::atoi(argv[++i]);
     else if (!std::strcmp(argv[i], "--quick")) { data_len = 409600; gemm_block = 8; }
@@ -158,21 +216,29 @@ int main(int argc, char **argv) {
     else if (!std::strcmp(argv[i], "--gemm-range") && i + 2 < argc) { gemm_lo = std::atoi(argv[++i]); gemm_hi = std::atoi(argv[++i]); }
     else if (!std::strcmp(argv[i], "--linear") && i + 3 < argc) { lin_m = std::atoi(argv[++i]); lin_n = std::atoi(argv[++i]); lin_k = std::atoi(argv[++i]); }
     else if (!std::strcmp(argv[i], "--pinned")) cux::Array4D::UsePinnedHostMemory(true);
+    else if (!std::strcmp(argv[i], "--gpus") && i + 1 < argc) gpus = std::atoi(argv[++i]);
+    else if (!std::strcmp(argv[i], "--multi-only")) multi_only = true;
   }
   cux::InitEnvironment();
   cux::QueryDevices();
-  std::printf("DotProductTest.\n");
-  DotProductTest(data_len);
-  std::printf("\n\nNorm2Test.\n");
-  Nrm2Test(data_len);
-  std::printf("\n\nGEMMTest.\n");
-  GEMMTest(gemm_block, gemm_lo, gemm_hi);
-  std::printf("\n\nReduceSumTest.\n");
-  ReduceSumTest(data_len);
-  std::printf("\n\nLinearInt8Test.\n");
-  LinearInt8Test(lin_m, lin_n, lin_k);
-  std::printf("\n\nScanTest.\n");
-  ScanTest(scan_len > 0 ? scan_len : data_len);
+  if (!multi_only) {
+    std::printf("DotProductTest.\n");
+    DotProductTest(data_len);
+    std::printf("\n\nNorm2Test.\n");
+    Nrm2Test(data_len);
+    std::printf("\n\nGEMMTest.\n");
+    GEMMTest(gemm_block, gemm_lo, gemm_hi);
+    std::printf("\n\nReduceSumTest.\n");
+    ReduceSumTest(data_len);
+    std::printf("\n\nLinearInt8Test.\n");
+    LinearInt8Test(lin_m, lin_n, lin_k);
+    std::printf("\n\nScanTest.\n");
+    ScanTest(scan_len > 0 ? scan_len : data_len);
+  }
+  if (gpus > 0) {
+    std::printf("\n\nMultiGpuTest (%d GPUs).\n", gpus);
+    MultiGpuTest(gpus, data_len, scan_len > 0 ? scan_len : data_len);
+  }
   cux::CleanUpEnvironment();
   std::printf("\ncux_demo: %s\n", g_failures ? "FAILED" : "all checks passed");
   return g_failures ? 1 : 0;

@@ -1,6 +1,7 @@
 // executor.hpp -- Executor and the environment functions
 // (0-frameworks/cux/include/executor.h:18-103, src/executor.cpp:10-89).
 #pragma once
+#include "cux/multi_executor.hpp"
 #include "cux/ops.hpp"
 
 namespace cux {

@@ -76,37 +76,87 @@ def scan_seed(dist, local_total, gathered=None):
     return wrap_i32(int(gathered[:rank].to(torch.int64).sum().item()))
 
 
+_TYPESTR = {torch.float32: "<f4", torch.float16: "<f2", torch.bfloat16: None, torch.int8: "|i1", torch.int16: "<i2",
+            torch.int32: "<i4", torch.int64: "<i8"}
+
+
+class _RawCuda:
+    """A raw device pointer dressed up for torch.as_tensor (zero copy, __cuda_array_interface__)."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
 class PeerExchange:
     """Per-rank exchange buffers for the fused multi-GPU kernels (cuxb_mg_*), one process per GPU.
 
-    Uses torch's symmetric memory (CUDA IPC / fabric handles under the hood) purely as the plumbing
-    that maps every rank's CUXB_MG_EXCHANGE_BYTES buffer into every process; the exchange itself is
-    done by the reduction kernel's finishing CTA with plain stores and loads on these pointers.
+    Plumbing only: every rank allocates its buffer with cuxb_malloc, exports it as a 64-byte handle
+    (cuxb_ipc_export), the handles travel through torch.distributed's all-gather, and every rank imports the
+    others' (cuxb_ipc_import) -- after which ptrs[r] is rank r's buffer as seen from this process.  The
+    exchange itself is done by the kernels with plain loads and stores on these pointers.  Where the
+    container does not allow CUDA IPC between the ranks, torch's symmetric memory provides the same mapping
+    (self.plumbing says which one is in use); the NVSwitch multicast route always needs it, because a
+    multicast address cannot be made from an IPC handle.
     """
 
     def __init__(self, dist, device):
-        import torch.distributed._symmetric_memory as symm
+        self.dist, self.device = dist, device
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
-        self.buf = symm.empty(64, dtype=torch.int64, device=device)  # 512 bytes >= CUXB_MG_EXCHANGE_BYTES
-        self.buf.zero_()
-        self.handle = symm.rendezvous(self.buf, dist.group.WORLD)
-        self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.plumbing = "cuxb_ipc_export / cuxb_ipc_import (CUDA IPC handles all-gathered through torch.distributed)"
+        self._keep = []
+        try:
+            self.buf = self._shared(torch.empty(64, dtype=torch.int64, device=device), use_ipc=True)
+        except Exception as ex:
+            self.plumbing = "torch symmetric memory (CUDA IPC unavailable here: %s)" % str(ex)[:120]
+            self.buf = self._shared(torch.empty(64, dtype=torch.int64, device=device), use_ipc=False)
+        self.ptrs = self.buf.ptrs
         torch.cuda.synchronize()
         dist.barrier()  # every buffer is zero before anybody's first exchange
 
-    def symmetric_like(self, t):
-        """A symmetric (peer-mapped) tensor with t's shape/dtype on every rank: .tensor is this rank's
-        instance, .ptrs[r] is rank r's instance as mapped into this process."""
-        import torch.distributed._symmetric_memory as symm
-        import torch.distributed as dist
+    def _shared(self, like, use_ipc):
+        """A zero-filled buffer of like's shape / dtype on every rank, mapped into every process."""
+        from . import capi
 
         class _Sym:
             pass
         out = _Sym()
-        out.tensor = symm.empty(tuple(t.shape), dtype=t.dtype, device=t.device)
-        out.handle = symm.rendezvous(out.tensor, dist.group.WORLD)
-        out.ptrs = [int(p) for p in out.handle.buffer_ptrs]
+        dist = self.dist
+        if use_ipc:
+            nbytes = max(256, like.numel() * like.element_size())
+            p = capi.dmalloc(nbytes)
+            capi.check(capi.lib().cuxb_memset(p, 0, nbytes, None), "cuxb_memset")
+            ok = torch.ones(1, device=self.device)
+            ptrs, err = [0] * self.world, None
+            try:
+                handles = [None] * self.world
+                dist.all_gather_object(handles, capi.ipc_export(p))
+                for r in range(self.world):
+                    ptrs[r] = p if r == self.rank else capi.ipc_import(handles[r])
+            except Exception as ex:
+                err = ex
+                ok.zero_()
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)    # all ranks take the same path
+            if float(ok[0]) == 0.0:
+                raise RuntimeError(str(err) if err else "a peer could not import the handle")
+            ts = _TYPESTR.get(like.dtype)
+            if ts is None:   # bf16 has no array-interface type string: view the bytes as int16
+                out.tensor = torch.as_tensor(_RawCuda(p, like.shape, "<i2"), device=self.device).view(like.dtype)
+            else:
+                out.tensor = torch.as_tensor(_RawCuda(p, like.shape, ts), device=self.device)
+            out.handle, out.ptrs = None, ptrs
+        else:
+            import torch.distributed._symmetric_memory as symm
+            out.tensor = symm.empty(tuple(like.shape), dtype=like.dtype, device=like.device)
+            out.tensor.zero_()
+            out.handle = symm.rendezvous(out.tensor, dist.group.WORLD)
+            out.ptrs = [int(x) for x in out.handle.buffer_ptrs]
+        self._keep.append(out)
         return out
+
+    def symmetric_like(self, t, need_multicast=False):
+        """A peer-mapped tensor with t's shape/dtype on every rank: .tensor is this rank's instance, .ptrs[r]
+        is rank r's instance as mapped into this process (.handle.multicast_ptr with need_multicast)."""
+        return self._shared(t, use_ipc=(not need_multicast) and self.plumbing.startswith("cuxb_ipc"))
 
     def route(self, ctx, B, mode):
         """How B reaches this rank in the fused-broadcast GEMMs.  Allocates a symmetric copy of B (the root
@@ -120,7 +170,9 @@ class PeerExchange:
         import torch.distributed as dist
         from . import capi
         r, w = self.rank, self.world
-        R = self.symmetric_like(B)
+        if mode == "mcast" and w < 3:
+            raise RuntimeError("multicast all-gather needs 3+ ranks (with two, the one receiver pulls from the root)")
+        R = self.symmetric_like(B, need_multicast=(mode == "mcast"))
         if r == 0:
             R.tensor.copy_(B)
         R.b_local = R.ptrs[r]
@@ -131,7 +183,8 @@ class PeerExchange:
             if w < 3:
                 raise RuntimeError("multicast all-gather needs 3+ ranks (with two, the one receiver pulls from the root)")
             mc = int(getattr(R.handle, "multicast_ptr", 0) or 0)
-            F = self.symmetric_like(torch.empty(capi.MG_MCAST_FLAGS_BYTES // 4, dtype=torch.int32, device=B.device))
+            F = self.symmetric_like(torch.empty(capi.MG_MCAST_FLAGS_BYTES // 4, dtype=torch.int32, device=B.device),
+                                    need_multicast=True)
             fmc = int(getattr(F.handle, "multicast_ptr", 0) or 0)
             if not mc or not fmc:
                 raise RuntimeError("no NVSwitch multicast mapping available for symmetric memory on this box")
@@ -165,23 +218,3 @@ class PeerExchange:
         torch.cuda.synchronize()
         dist.barrier()
         return R
-
-    def chain(self, ctx, b_like):
-        """Set up the chained broadcast (cuxb_mg_set_chain) for ctx: a symmetric copy of B and symmetric
-        flags; rank r pulls from rank r - 1.  Returns (bsym, upstream_ptr): bsym.tensor is this rank's B
-        (the root fills it), upstream_ptr the B to pass as b_root / bt_root."""
-        import torch
-        import torch.distributed as dist
-        from . import capi
-        bsym = self.symmetric_like(b_like)
-        fsym = self.symmetric_like(torch.empty(capi.MG_CHAIN_FLAGS_BYTES // 4, dtype=torch.int32, device=b_like.device))
-        fsym.tensor.zero_()
-        torch.cuda.synchronize()
-        dist.barrier()
-        r, w = self.rank, self.world
-        src, up, down = chain_plan(w, r)
-        if r > 0 and w > 2:   # with two ranks the chain is the star: no flags needed
-            ctx.mg_set_chain(fsym.ptrs[r], fsym.ptrs[up] if up is not None else 0,
-                             fsym.ptrs[down] if down is not None else 0)
-        bsym.flags = fsym
-        return bsym, bsym.ptrs[src if src is not None else 0]

@@ -240,6 +240,47 @@ int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *flags_up, co
 int cuxb_mg_set_multicast(cuxb_ctx *ctx, int world, int rank, void *flags_local, void *flags_mc, void *b_mc);
 int cuxb_enable_peer_access(int device, int peer_device);
 
+/* ---- the multi-GPU driver: ONE host thread driving g GPUs of one NVLink box.  cux::Executor::Initialize(dev)
+ * (0-frameworks/cux/src/executor.cpp:10-22) generalised to g devices, for the master / worker flow of
+ * mpi/alg_matrix_multiply.cpp:52-80 (row blocks of A and C per worker, one B, results gathered and checked)
+ * without MPI.  cuxb_mg_create(ndev, devices, &mg) -- devices == NULL means 0..ndev-1 -- creates one cuxb_ctx and one stream
+ * per device, enables peer access between all pairs, allocates the exchange buffers, the broadcast flags
+ * and (on demand) every rank's copy of B, loads the kernels on every device before any of them can wait on
+ * a peer, and routes the broadcast (2 GPUs: pull from the root; more: rank r pulls from rank r-1).
+ * The cuxb_mg_all_* calls take ARRAYS indexed by rank -- sizes and pointers to memory on that rank's GPU --
+ * and issue one asynchronous launch per device on that device's stream; cuxb_mg_sync waits for all.  Rank r
+ * holds the r-th contiguous slice of a vector, or M[r] rows of A and C; B (Bt) lives on rank 0 only and is
+ * delivered inside the GEMM kernels.  Reductions leave the same scalar at every res[r].  Not thread-safe:
+ * one host thread per cuxb_mg.  The caller's current device is changed by these calls. */
+typedef struct cuxb_mg cuxb_mg;
+int cuxb_mg_create(int ndev, const int *devices, cuxb_mg **out);
+int cuxb_mg_destroy(cuxb_mg *mg);
+int cuxb_mg_world(const cuxb_mg *mg);
+int cuxb_mg_device(const cuxb_mg *mg, int rank);
+cuxb_ctx *cuxb_mg_ctx(cuxb_mg *mg, int rank);   /* owned by mg */
+void *cuxb_mg_stream(cuxb_mg *mg, int rank);    /* the stream the cuxb_mg_all_* launches of this rank go to */
+int cuxb_mg_sync(cuxb_mg *mg);
+int cuxb_mg_all_dot_f32(cuxb_mg *mg, const long long *n, const float *const *a, const float *const *b, float *const *res);
+int cuxb_mg_all_sum_f32(cuxb_mg *mg, const long long *n, const float *const *x, float *const *res);
+int cuxb_mg_all_nrm2_f32(cuxb_mg *mg, const long long *n, const float *const *x, float *const *res);
+int cuxb_mg_all_scan_i32(cuxb_mg *mg, const long long *n, const int32_t *const *in, int32_t *const *out);
+int cuxb_mg_all_sgemm_f32(cuxb_mg *mg, const int *M, int N, int K, float alpha, const float *const *A, int lda,
+                          const float *B_root, int ldb, float beta, float *const *C, int ldc);
+int cuxb_mg_all_hgemm_f16_f32acc(cuxb_mg *mg, const int *M, int N, int K, float alpha, const void *const *A, int lda,
+                                 const void *B_root, int ldb, float beta, void *const *C, int ldc, int c_dtype);
+int cuxb_mg_all_linear_s8_s32(cuxb_mg *mg, const int *M, int N, int K, const int8_t *const *A, const int8_t *Bt_root,
+                              int32_t *const *C);
+
+/* ---- one PROCESS per GPU (torchrun, MPI): the peer pointers the cuxb_mg_* kernel entry points take are made
+ * by exporting a cuxb_malloc'ed buffer as a 64-byte handle, passing the handle to the other processes over
+ * whatever channel the launcher offers (an all-gather of bytes), and importing it there.  Thin wrappers of
+ * cudaIpcGetMemHandle / cudaIpcOpenMemHandle / cudaIpcCloseMemHandle; the buffer must be a whole cuxb_malloc
+ * allocation.  The counterpart of the MPI_Send / MPI_Recv plumbing of mpi/alg_matrix_multiply.cpp:57-72. */
+#define CUXB_IPC_HANDLE_BYTES 64
+int cuxb_ipc_export(void *dptr, void *handle_out);
+int cuxb_ipc_import(const void *handle, void **dptr_out);
+int cuxb_ipc_close(void *dptr);
+
 /* ---- GEMM: C = alpha * A[M,K] * B[K,N] + beta * C, row-major.
  *
  * cuxb_sgemm_f32 replaces GemmGpuKernelIF::func for TypeFlag::FLOAT32

@@ -54,3 +54,23 @@ def test_reference_data_test_cases_on_the_device():
     r = subprocess.run([exe], capture_output=True, text=True, timeout=200)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "cux_device_test: all passed" in r.stdout and "FAILED" not in r.stdout
+
+
+def _gpu_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("gpus", [1, 2])
+def test_demo_multi_gpu_executor(gpus):
+    """cux::MultiExecutor (Executor::Initialize generalised to g devices over the C ABI's cuxb_mg driver): dot and
+    scan over contiguous slices, gemm over row blocks with B on rank 0 only -- mpi/alg_matrix_multiply.cpp:52-80's
+    flow -- checked by cux's ResultChecker against the host kernels.  One GPU is the degenerate world of one."""
+    if _gpu_count() < gpus:
+        pytest.skip("needs %d GPUs" % gpus)
+    r = run_demo("--quick", "--multi-only", "--gpus", str(gpus))
+    out = r.stdout
+    assert r.returncode == 0, out[-3000:] + r.stderr[-2000:]
+    assert "cux_demo: all checks passed" in out and "FAIL" not in out and "Fail" not in out
+    for what in ("multi-GPU dot", "multi-GPU gemm fp32", "multi-GPU scan_i32"):
+        assert what in out, what

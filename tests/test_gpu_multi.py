@@ -272,3 +272,93 @@ def test_fused_exchange_replayed_from_cuda_graphs():
         for r in range(world):
             assert float(res[r][0]) == float(want_dot), (rep, r)
         assert np.array_equal(np.concatenate([o.cpu().numpy() for o in out]), want_scan), rep
+
+
+def test_mg_driver_two_gpus_all_ops():
+    """cuxb_mg_create: the C-ABI driver that owns contexts, streams, peer access, exchange buffers, flags and
+    the copies of B -- the flow of mpi/alg_matrix_multiply.cpp:52-80 (row blocks of A and C, one B, results
+    gathered and checked) from one host thread, nothing but C calls."""
+    world = 2
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs" % world)
+    mg = capi.MultiGpu(range(world))
+    dev = lambda x, r: torch.from_numpy(np.ascontiguousarray(x)).to("cuda:%d" % r)
+    # reductions + scan over an uneven split
+    n = 2_000_003
+    a, b = dg.int_fill(n, -2, 2, tag=501), dg.int_fill(n, -2, 2, tag=502)
+    x = dg.int_fill(n, -3, 3, np.int32, tag=503)
+    spans = [multi.shard_range(n, world, r) for r in range(world)]
+    da = [dev(a[lo:hi], r) for r, (lo, hi) in enumerate(spans)]
+    db = [dev(b[lo:hi], r) for r, (lo, hi) in enumerate(spans)]
+    dx = [dev(x[lo:hi], r) for r, (lo, hi) in enumerate(spans)]
+    res = [torch.zeros(1, device="cuda:%d" % r) for r in range(world)]
+    out = [torch.empty_like(t) for t in dx]
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    lens = [hi - lo for lo, hi in spans]
+    P = lambda ts: [t.data_ptr() for t in ts]
+    for rep in range(2):
+        mg.all_dot_f32(lens, P(da), P(db), P(res))
+        mg.sync()
+        assert all(float(t[0]) == float(oracle.dot_f32(a, b)) for t in res)
+    mg.all_sum_f32(lens, P(da), P(res))
+    mg.sync()
+    assert all(float(t[0]) == float(oracle.sum_f32(a)) for t in res)
+    mg.all_nrm2_f32(lens, P(da), P(res))
+    mg.sync()
+    assert all(float(t[0]) == float(oracle.nrm2_f32(a)) for t in res)
+    mg.all_scan_i32(lens, P(dx), P(out))
+    mg.sync()
+    assert np.array_equal(np.concatenate([o.cpu().numpy() for o in out]), oracle.scan_i32(x))
+    # row-sharded GEMMs, B on rank 0 only
+    M, N, K = 256, 512, 384
+    A = [dg.int_fill((M, K), -2, 5, tag=510 + r) for r in range(world)]
+    B = dg.int_fill((K, N), -2, 5, tag=515)
+    dA, dB = [dev(A[r], r) for r in range(world)], dev(B, 0)
+    dC = [torch.zeros((M, N), device="cuda:%d" % r) for r in range(world)]
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    for rep in range(2):
+        mg.all_sgemm_f32([M] * world, N, K, 1.0, P(dA), K, dB.data_ptr(), N, 0.0, P(dC), N)
+        mg.sync()
+        for r in range(world):
+            want = oracle.gemm_f32(A[r], B, np.zeros((M, N), np.float32), 1.0, 0.0, order="ikj", threads=8)
+            assert np.array_equal(dC[r].cpu().numpy(), want), (r, rep)
+    A16 = [oracle.f32_to_f16(dg.int_fill((M, K), -10, 9, tag=520 + r)) for r in range(world)]
+    B16 = oracle.f32_to_f16(dg.int_fill((K, N), -10, 9, tag=525))
+    dA16 = [dev(A16[r].view(np.int16), r) for r in range(world)]
+    dB16 = dev(B16.view(np.int16), 0)
+    dC16 = [torch.zeros((M, N), dtype=torch.int16, device="cuda:%d" % r) for r in range(world)]
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    mg.all_hgemm_f16([M] * world, N, K, 1.0, P(dA16), K, dB16.data_ptr(), N, 0.0, P(dC16), N, capi.FLOAT16)
+    mg.sync()
+    for r in range(world):
+        assert np.array_equal(dC16[r].cpu().numpy().view(np.uint16), oracle.hgemm_f16(A16[r], B16, threads=8)), r
+    A8 = [dg.int_fill((M, K), -128, 127, tag=530 + r).astype(np.int8) for r in range(world)]
+    Bt = dg.int_fill((N, K), -128, 127, tag=535).astype(np.int8)
+    dA8, dBt = [dev(A8[r], r) for r in range(world)], dev(Bt, 0)
+    dC8 = [torch.zeros((M, N), dtype=torch.int32, device="cuda:%d" % r) for r in range(world)]
+    for r in range(world):
+        torch.cuda.synchronize(r)
+    mg.all_linear_s8([M] * world, N, K, P(dA8), dBt.data_ptr(), P(dC8))
+    mg.sync()
+    for r in range(world):
+        assert np.array_equal(dC8[r].cpu().numpy(), oracle.linear_s8(A8[r], Bt, threads=8)), r
+    mg.close()
+
+
+def test_mg_driver_single_gpu_and_argument_errors():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    with pytest.raises(capi.CuxbError):
+        capi.MultiGpu([0, 0])          # one rank per GPU
+    with pytest.raises(capi.CuxbError):
+        capi.MultiGpu([99])
+    mg = capi.MultiGpu([0])            # a world of one degenerates to the single-GPU kernels
+    x = torch.ones(1000, device="cuda:0")
+    r = torch.zeros(1, device="cuda:0")
+    mg.all_sum_f32([1000], [x.data_ptr()], [r.data_ptr()])
+    mg.sync()
+    assert float(r[0]) == 1000.0
+    mg.close()
