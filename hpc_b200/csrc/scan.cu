@@ -8,8 +8,8 @@
 //
 // One pass over the data: the input is cut into tiles of 8192 elements; a persistent
 // grid of one resident CTA per SM walks the tiles round-robin (so a CTA only ever waits
-// on tiles owned by CTAs that are running).  cp.async streams tiles into a 128 KiB
-// shared-memory ring three passes ahead; a tile is scanned in registers (shuffle
+// on tiles owned by CTAs that are running).  cp.async streams tiles into a 192 KiB
+// shared-memory ring two passes ahead; a tile is scanned in registers (shuffle
 // scans), its aggregate is published in a 64-bit state word, and its exclusive prefix
 // is the CTA's own running prefix plus the aggregates of the tiles in between (see
 // "Prefix gathering" below) -- fetched one pass late so the L2 round trip is hidden.
@@ -466,8 +466,10 @@ int scan_smem_bytes() { return kScanSmemBytes; }
 // application which has already handed all device memory to its own pool, a service with a fixed
 // memory budget where a late cudaMalloc may fail, or a latency-sensitive loop that cannot afford
 // the device-wide synchronisation an allocation implies.  For them the scratch lives in the
-// file-scope array below.  It is part of the library image, so every GPU that loads libcuxb.so
-// holds these ~128 KiB until the process exits, whether or not the entry point is ever called.
+// file-scope array below.  It is part of the library image: every GPU on which this library's device
+// code gets loaded holds these ~128 KiB until the process exits.  (CUDA loads device code lazily by
+// default, so that happens at the first call on the device, not when libcuxb.so is opened -- which is
+// why that first call should be made early, while memory is still available; see cuxb.h.)
 //
 // Size limit: kNoAllocMaxElems elements.  The array holds one state word per 4096 elements of that
 // limit; the kernel's tiles are at least that large, so a call uses a prefix of the array.

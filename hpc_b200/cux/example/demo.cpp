@@ -127,6 +127,21 @@ void LinearInt8Test(int M, int N, int K) {
   Finish(ex, "linear_int8");
 }
 
+void LinearBf16Test(int M, int N, int K) {
+  // LinearNormalBf16 (simd/x86/linear.cpp:137-151) on the host vs the tcgen05 kernel with bf16 operands.  With
+  // the integer fill every fp32 partial sum is exact, so both sides round the same value to bf16 once.
+  cux::Executor ex;
+  ex.Initialize(0);
+  ex.SelectOp("linear_bf16", "");
+  cux::Array4D a(1, 1, M, K), bt(1, 1, N, K), c(1, 1, M, N);
+  Bind(ex, {&a, &bt}, {&c}, -8, 8);
+  std::vector<cux::bfloat16> host;
+  if (!g_device_only) { ex.Run(cux::OpRunMode::ON_HOST); host = Snapshot<cux::bfloat16>(&c); }
+  ex.Run(cux::OpRunMode::ON_DEVICE);
+  if (!g_device_only) CrossCheck("linear_bf16", host, Snapshot<cux::bfloat16>(&c));
+  Finish(ex, "linear_bf16");
+}
+
 void ScanTest(int n) {
   cux::Executor ex;
   ex.Initialize(0);
@@ -232,6 +247,8 @@ int main(int argc, char **argv) {
     ReduceSumTest(data_len);
     std::printf("\n\nLinearInt8Test.\n");
     LinearInt8Test(lin_m, lin_n, lin_k);
+    std::printf("\n\nLinearBf16Test.\n");
+    LinearBf16Test(lin_m, lin_n, lin_k);
     std::printf("\n\nScanTest.\n");
     ScanTest(scan_len > 0 ? scan_len : data_len);
   }

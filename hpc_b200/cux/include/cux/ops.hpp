@@ -96,6 +96,23 @@ private:
   Array4D *A_ = nullptr, *Bt_ = nullptr, *C_ = nullptr;
 };
 
+// bf16 linear (LinearNormalBf16 / LinearAvx512Bf16, simd/x86/linear.cpp:137-182): C[M,N] bf16 = bf16 of the
+// fp32 sum over k of A[M,K] * Bt[N,K], all three matrices stored as bf16.  Same kernel interface shape as
+// linear_int8 (untyped pointers), so plugins are LinearI8*KernelIF structs with type_flag BFLOAT16.
+class LinearBf16 : public Operator, protected KernelLists<LinearI8CpuKernelIF, LinearI8GpuKernelIF> {
+public:
+  explicit LinearBf16(OpAssistor *assistor);
+  static Operator *Creator(OpAssistor *assistor, std::string &params_str);
+  void Help() const override;
+  void AddPlugin(KernelInterface *kernel_if, OpRunMode mode) override;
+  void ExtractDataTypes(std::vector<int> &type_flags) override;
+  void RunOnHost(const std::vector<Array4D *> &input, const std::vector<Array4D *> &output) override;
+  void RunOnDevice(const std::vector<Array4D *> &input, const std::vector<Array4D *> &output) override;
+private:
+  void IoCheckAndSet(const std::vector<Array4D *> &input, const std::vector<Array4D *> &output) override;
+  Array4D *A_ = nullptr, *Bt_ = nullptr, *C_ = nullptr;
+};
+
 class ScanI32 : public Operator, protected KernelLists<ScanCpuKernelIF, ScanGpuKernelIF> {
 public:
   explicit ScanI32(OpAssistor *assistor);

@@ -14,6 +14,7 @@ void InitEnvironment() {
     f.RegisterOpClass("gemm", Gemm::Creator);
     f.RegisterOpClass("reduce_sum", ReduceSum::Creator);
     f.RegisterOpClass("linear_int8", LinearInt8::Creator);
+    f.RegisterOpClass("linear_bf16", LinearBf16::Creator);
     f.RegisterOpClass("scan_i32", ScanI32::Creator);
     registered = true;
   }

@@ -547,6 +547,108 @@ void LinearInt8::RunOnDevice(const std::vector<Array4D *> &input, const std::vec
   for (size_t ki = 0; ki < gpu_kernels_.size(); ki++) PrintRecordedInfo(OpRunMode::ON_DEVICE, (int)ki, gpu_kernels_[ki]);
 }
 
+// =====================================================================================  linear_bf16
+LinearBf16::LinearBf16(OpAssistor *assistor) : Operator(assistor) {
+  {  // host V0: LinearNormalBf16 (simd/x86/linear.cpp:137-151): fp32 accumulate over k in order, one rounding to bf16
+    auto *k = new LinearI8CpuKernelIF();
+    k->type_flag = TypeFlag::BFLOAT16;
+    k->describe_info = "Normal";
+    k->func = [](int M, int N, int K, const void *vA, const void *vB, void *vC) {
+      const bfloat16 *A = static_cast<const bfloat16 *>(vA), *B = static_cast<const bfloat16 *>(vB);
+      bfloat16 *C = static_cast<bfloat16 *>(vC);
+      for (int r = 0; r < M; r++)
+        for (int c = 0; c < N; c++) {
+          float acc = 0.f;
+          const bfloat16 *a = A + (size_t)r * K, *b = B + (size_t)c * K;
+          for (int k2 = 0; k2 < K; k2++) acc += (float)a[k2] * (float)b[k2];
+          C[(size_t)r * N + c] = bfloat16(acc);
+        }
+    };
+    cpu_kernels_.push_back(k);
+  }
+  {
+    auto *k = new LinearI8GpuKernelIF();
+    OpAssistor *as = assistor_;
+    k->type_flag = TypeFlag::BFLOAT16;
+    k->describe_info = "cuxb sm_100a: TMA -> tcgen05.mma kind::f16 bf16 operands (2-CTA 256x256x16) -> TMEM fp32 -> bf16 C";
+    k->get_config = [](int M, int N) {
+      Config2D c;
+      c.virtual_thread_count = dim3(N, M, 1);
+      c.threads_per_block = dim3(256, 1, 1);
+      c.blocks_per_grid = dim3(DivUp(N, 256), DivUp(M, 256), 1);
+      return c;
+    };
+    k->func = [as](Config2D, int M, int N, int K, const void *A, const void *Bt, void *C) {
+      DEVICE_CALL(cuxb_linear_bf16_f32acc(as->ctx(), nullptr, M, N, K, A, Bt, C, CUXB_BFLOAT16));
+    };
+    k->config_kernel = nullptr;
+    gpu_kernels_.push_back(k);
+  }
+  ResetByKernelNum(cpu_kernels_.size(), gpu_kernels_.size());
+}
+Operator *LinearBf16::Creator(OpAssistor *assistor, std::string &) { return new LinearBf16(assistor); }
+void LinearBf16::Help() const {
+  CUXLOG_COUT("***************** Op Helper ********************");
+  CUXLOG_COUT("* Name: LinearBf16.");
+  CUXLOG_COUT("* Function: C(M, N) bf16 = A(M, K) bf16 * Bt(N, K)^T bf16, fp32 accumulate");
+  CUXLOG_COUT("* Inputs:  [Two] Array4D: A with (height, width) = (M, K), Bt with (N, K). ");
+  CUXLOG_COUT("* Outputs: [One] Array4D with (M, N).");
+  CUXLOG_COUT("**************************************************");
+}
+void LinearBf16::IoCheckAndSet(const std::vector<Array4D *> &in, const std::vector<Array4D *> &out) {
+  if (in.size() != 2 || out.size() != 1) { Help(); CUXLOG_ERR("The dimensions of the data do not match."); }
+  const std::vector<int> a = in[0]->shape(), b = in[1]->shape(), c = out[0]->shape();
+  if (a[WIDTH] != b[WIDTH] || a[HEIGHT] != c[HEIGHT] || b[HEIGHT] != c[WIDTH]) { Help(); CUXLOG_ERR("The dimensions of the data do not match."); }
+  A_ = in[0], Bt_ = in[1], C_ = out[0];
+}
+void LinearBf16::AddPlugin(KernelInterface *kernel_if, OpRunMode mode) {
+  if (mode == OpRunMode::ON_HOST) cpu_kernels_.push_back(static_cast<LinearI8CpuKernelIF *>(kernel_if));
+  else gpu_kernels_.push_back(static_cast<LinearI8GpuKernelIF *>(kernel_if));
+  ResetByKernelNum(cpu_kernels_.size(), gpu_kernels_.size());
+}
+void LinearBf16::ExtractDataTypes(std::vector<int> &type_flags) { MarkTypes(type_flags, {BFLOAT16}); }
+void LinearBf16::RunOnHost(const std::vector<Array4D *> &input, const std::vector<Array4D *> &output) {
+  CUXLOG_COUT("LinearBf16 -> CPU: ");
+  IoCheckAndSet(input, output);
+  const int M = A_->shape()[HEIGHT], K = A_->shape()[WIDTH], N = Bt_->shape()[HEIGHT];
+  for (size_t ki = 0; ki < cpu_kernels_.size(); ki++) {
+    LinearI8CpuKernelIF *kernel = cpu_kernels_[ki];
+    const void *A = nullptr, *B = nullptr;
+    bfloat16 *C = nullptr;
+    cpu_timer_record_[ki].input = GET_TIME_DIFF(cpu_timer_, {
+      A = A_->GetCpuData<bfloat16>(PUSH_IF_EMPTY);
+      B = Bt_->GetCpuData<bfloat16>(PUSH_IF_EMPTY);
+      C = C_->GetCpuData<bfloat16>(NO_PUSH);
+    });
+    cpu_timer_record_[ki].run = GET_TIME_DIFF(cpu_timer_, kernel->func(M, N, K, A, B, C););
+    assistor_->checker()->CheckArray(C, C_->num_element(), 1.0f / C_->num_element(), (int)ki);
+  }
+  for (size_t ki = 0; ki < cpu_kernels_.size(); ki++) PrintRecordedInfo(OpRunMode::ON_HOST, (int)ki, cpu_kernels_[ki]);
+}
+void LinearBf16::RunOnDevice(const std::vector<Array4D *> &input, const std::vector<Array4D *> &output) {
+  CUXLOG_COUT("LinearBf16 -> GPU: ");
+  IoCheckAndSet(input, output);
+  const int M = A_->shape()[HEIGHT], K = A_->shape()[WIDTH], N = Bt_->shape()[HEIGHT];
+  for (size_t ki = 0; ki < gpu_kernels_.size(); ki++) {
+    LinearI8GpuKernelIF *kernel = gpu_kernels_[ki];
+    Config2D config = kernel->get_config(M, N);
+    QueryPotentialOccupancy(kernel->config_kernel, (int)ki, config.threads_per_block.x, config.shared_memory_size);
+    const void *A = nullptr, *B = nullptr;
+    void *C = nullptr;
+    gpu_timer_record_[ki].input = GET_TIME_DIFF(gpu_timer(), {
+      A = A_->GetGpuData<bfloat16>(PUSH_IF_EMPTY);
+      B = Bt_->GetGpuData<bfloat16>(PUSH_IF_EMPTY);
+      C = C_->GetGpuData<bfloat16>(NO_PUSH);
+    });
+    gpu_timer_record_[ki].warnup = GET_TIME_DIFF(gpu_timer(), kernel->func(config, M, N, K, A, B, C););
+    CUXB_CHECK(cuxb_memset(C, 0xff, (size_t)C_->num_element() * 2, nullptr));  // the timed run must rewrite every element
+    gpu_timer_record_[ki].run = GET_TIME_DIFF(gpu_timer(), kernel->func(config, M, N, K, A, B, C););
+    gpu_timer_record_[ki].output = GET_TIME_DIFF(gpu_timer(), { C_->GetCpuData<bfloat16>(PUSH); });
+    assistor_->checker()->CheckArray(C_->GetCpuData<bfloat16>(NO_PUSH), C_->num_element(), 1.0f / C_->num_element(), (int)ki);
+  }
+  for (size_t ki = 0; ki < gpu_kernels_.size(); ki++) PrintRecordedInfo(OpRunMode::ON_DEVICE, (int)ki, gpu_kernels_[ki]);
+}
+
 // =====================================================================================  scan_i32
 ScanI32::ScanI32(OpAssistor *assistor) : Operator(assistor) {
   {  // host V0: VectorScanNormal's recurrence (simd/x86/vector_scan.cpp:21-26) on int32, wrap-around adds

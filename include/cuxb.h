@@ -32,14 +32,18 @@
  *     cheap (a few KiB of device memory until a workspace is first needed).
  *     Calls may come from any host thread, but not from two at once for the
  *     same context, except the *_host entry points, which serialise
- *     themselves.
+ *     themselves.  An entry point that takes a context makes that context's
+ *     device the calling thread's current device and leaves it so.
  *   - CUDA graphs: the single-GPU kernel entry points (reductions, scans
  *     including cuxb_scan_i32_noalloc, GEMMs, linears, convert, fill) may be
  *     recorded by stream capture and replayed: no protocol state is baked
  *     into a launch's arguments (the scan counts its epoch on the device, the
  *     reduction and split-K tickets reset themselves).  Call once outside the
  *     capture first, so that workspaces exist and nothing allocates while
- *     capturing.  The multi-GPU reductions and scan (cuxb_mg_dot_f32 ...
+ *     capturing.  A recorded launch holds the ADDRESS of the context's workspace: a later call on the same
+ *     context that needs a larger one (a longer scan, a split-K GEMM with more tiles, larger *_host
+ *     staging) frees and reallocates it, after which graphs recorded before must not be replayed --
+ *     make the largest call first, or record again.  The multi-GPU reductions and scan (cuxb_mg_dot_f32 ...
  *     cuxb_mg_scan_i32) can be captured too: their exchange epoch is counted
  *     in the exchange buffer.  NOT capturable: the *_host entry points (they
  *     synchronise) and the fused-broadcast GEMMs (cuxb_mg_*gemm*,
@@ -144,8 +148,16 @@ int cuxb_scan_f32(cuxb_ctx *ctx, void *stream, long long n, const float *in, flo
  * creating one allocates -- and runs on the current device, keeping its tile-state scratch in a static
  * array inside the library (about 128 KiB per GPU, held from library load to process exit).
  * Limit: n <= 67,108,864 (2^26) elements; larger n returns CUXB_ERR_TOO_LARGE.  The first call on each
- * device resolves the array's device address; make it before any stream capture starts.  Calls on the
- * same GPU share the scratch, so two calls whose kernels may run at the same time race. */
+ * device resolves the array's device address; make it before any stream capture starts -- and make it
+ * EARLY: CUDA loads a library's device code lazily by default, so it is this first call (not the loading
+ * of libcuxb.so) that brings the kernel and the array onto the GPU, and that one-off step does need a few
+ * hundred KiB of device memory.  A host application that is about to hand all remaining memory to its own
+ * pool should therefore make one small warm-up call per device first (or run with
+ * CUDA_MODULE_LOADING=EAGER); every later call leaves the amount of free device memory unchanged
+ * (tests/test_zz_no_alloc.py checks exactly that).  It runs on the CURRENT device: the other entry points
+ * switch the calling thread's current device to their context's and do not switch back, so after calls on
+ * several GPUs set the device (cuxb_set_device) before calling this one.  Calls on the same GPU share the
+ * scratch, so two calls whose kernels may run at the same time race. */
 int cuxb_scan_i32_noalloc(void *stream, long long n, const int32_t *in, int32_t *out, int32_t seed);
 
 /* ---- multi-GPU (one process or thread per GPU, all on one NVLink/NVSwitch box).  The scalar

@@ -27,7 +27,7 @@ def test_demo_reference_shapes():
     assert r.returncode == 0, out[-3000:] + r.stderr[-2000:]
     assert "cux_demo: all checks passed" in out
     assert "Fail" not in out
-    for name in ("dot", "nrm2", "gemm fp32", "reduce_sum", "linear_int8", "scan_i32"):
+    for name in ("dot", "nrm2", "gemm fp32", "reduce_sum", "linear_int8", "linear_bf16", "scan_i32"):
         assert "host V0 vs device V0 (%s): 0 of" % name in out, name
     assert out.count("Pass: V0 vs V") >= 3  # plugin kernels and the fp16 tcgen05 kernel vs device V0
     assert "tcgen05" in out and "Plugin example" in out
