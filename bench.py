@@ -1119,7 +1119,8 @@ def main():
             "verified": primary["verified"], "verification": primary["verification"], "all_verified": all_ok,
             "variants": primary.get("variants"), "weak": primary.get("weak"),
             "second_data_set": primary.get("second_data_set"), "device_result": primary["device_result"],
-            "probes": env["probes"] or None, "nvlink_probe": nvlink_probe, "also": also,
+            "probes": env["probes"] or None, "nvlink_probe": nvlink_probe,
+            "peer_plumbing": getattr(peers, "plumbing", None), "also": also,
         }
         print(json.dumps(line))
         sys.stdout.flush()

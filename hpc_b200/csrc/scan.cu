@@ -142,14 +142,20 @@ __device__ __forceinline__ long long tile_elem_base(unsigned int tile) {
 
 // Shared-memory ring (kScanRing tile slots, see the pipeline description further down): every scan
 // thread owns the same four 16-byte chunks of each slot -- filled by its own cp.async, read, rewritten
-// and read again by itself only.  Layout [slot][j][thread]: conflict-free for the async writes and for
-// LDS.128 / STS.128.
+// and read again by itself only.  Layout: see slot_chunk().
+// uint4 index of this thread's chunk j of ring slot `slot`: the slot holds the tile in GLOBAL order (warp w's
+// 512 elements are 2 KiB contiguous, as in memory), so a warp's share of a finished tile can leave with one
+// bulk copy.  A warp instruction touches 32 consecutive 16-byte chunks: conflict-free.
+__device__ __forceinline__ int slot_chunk(int slot, int j) {
+  return slot * (kScanTileElems / 4) + (threadIdx.x >> 5) * 128 + j * 32 + (threadIdx.x & 31);
+}
+
 template <typename T>
 __device__ __forceinline__ void prefetch_tile(uint4 *ring, int slot, const T *in, unsigned int tile) {
   const long long base = tile_elem_base(tile);
 #pragma unroll
   for (int j = 0; j < 4; j++) {
-    const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (slot * 4 + j) * kScanThreads + threadIdx.x);
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + slot_chunk(slot, j));
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(in + base + j * 128) : "memory");
   }
 }
@@ -199,6 +205,10 @@ constexpr int BAR_PREFIX = 2;                        // (+ pass % 4) the tile's 
 #ifndef CUXB_SCAN_STORE_LAG
 #define CUXB_SCAN_STORE_LAG 3
 #endif
+#ifndef CUXB_SCAN_BULK_STORE
+#define CUXB_SCAN_BULK_STORE 1
+#endif
+constexpr bool kBulkStore = CUXB_SCAN_BULK_STORE != 0;   // finished tiles leave shared memory by cp.async.bulk
 constexpr int kPrefetch = CUXB_SCAN_PREFETCH, kGatherLag = CUXB_SCAN_GATHER_LAG, kStoreLag = CUXB_SCAN_STORE_LAG;
 constexpr int kScanRing = kPrefetch + kStoreLag + 1;
 static_assert(kStoreLag > kGatherLag, "a tile's prefix must be settled before the pass that stores it");
@@ -283,7 +293,7 @@ scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed
   auto is_async = [&](int q) {
     return vec_ok && q < passes && (long long)(tile_of(q) + 1) * kScanTileElems <= n;
   };
-  auto slot_ptr = [&](int slot, int j) { return ring + (slot * 4 + j) * kScanThreads + threadIdx.x; };
+  auto slot_ptr = [&](int slot, int j) { return ring + slot_chunk(slot, j); };
   // add the settled prefix to a parked tile and write it out
   auto finish_tile = [&](int q, int slot) {
     named_bar_sync(BAR_PREFIX + (q & 3), kScanCtaThreads);
@@ -294,7 +304,36 @@ scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed
       const V t = *reinterpret_cast<const V *>(slot_ptr(slot, j));
       r.v[j][0] = t.x, r.v[j][1] = t.y, r.v[j][2] = t.z, r.v[j][3] = t.w;
     }
-    store_tile(r, add, out, n, tile_of(q), vec_ok);
+    const unsigned int tile = tile_of(q);
+    if (kBulkStore && vec_ok && (long long)(tile + 1) * kScanTileElems <= n) {
+      // add the prefix in place, then ONE bulk copy per warp moves its 2 KiB of the tile to global memory:
+      // the copy engine streams it out while the warp is already scanning the next tile (128 STG.128 per
+      // warp and tile became one instruction).  Only this warp ever touches this part of the slot, so a
+      // warp-level barrier is all the ordering the generic-proxy writes need before the async-proxy read.
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        V t;
+        t.x = r.v[j][0] + add, t.y = r.v[j][1] + add, t.z = r.v[j][2] + add, t.w = r.v[j][3] + add;
+        *reinterpret_cast<V *>(slot_ptr(slot, j)) = t;
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        const unsigned src = (unsigned)__cvta_generic_to_shared(ring + slot * (kScanTileElems / 4) + warp * 128);
+        T *dst = out + (long long)tile * kScanTileElems + warp * 512;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], 2048;" ::"l"(dst), "r"(src) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    } else {
+      store_tile(r, add, out, n, tile, vec_ok);
+    }
+  };
+  // before a slot is refilled, the bulk copy that emptied it (issued a whole pass earlier) must have read it
+  auto slot_reusable = [&]() {
+    if (kBulkStore) {
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      __syncwarp();
+    }
   };
   auto next_slot = [](int s) { return s + 1 == kScanRing ? 0 : s + 1; };
 
@@ -309,7 +348,10 @@ scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed
   // ring positions: tile p sits in slot p % kScanRing (kept as counters -- no division in the loop)
   int slot_cur = 0, slot_pf = kPrefetch % kScanRing, slot_st = (kScanRing - kStoreLag) % kScanRing;
   for (int p = 0; p < passes; p++) {
-    if (is_async(p + kPrefetch)) prefetch_tile(ring, slot_pf, in, tile_of(p + kPrefetch));
+    if (is_async(p + kPrefetch)) {
+      slot_reusable();
+      prefetch_tile(ring, slot_pf, in, tile_of(p + kPrefetch));
+    }
     asm volatile("cp.async.commit_group;" ::: "memory");
 
     // ---- fetch this tile into registers
@@ -365,6 +407,7 @@ scan_kernel(const T *in, T *out, long long n, T seed, const T *__restrict__ seed
     const int q = passes - d;
     if (q >= 0) finish_tile(q, q % kScanRing);
   }
+  if (kBulkStore && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // shared memory stays valid until read
   // This CTA's helper warp settled its last tile before the store above could run, so the CTA no
   // longer reads anybody's state words.  The last CTA through here opens the next epoch.
   if (threadIdx.x == 0) {

@@ -49,6 +49,7 @@ struct UmmaArgs {
   int tiles_m, tiles_n;  // in units of (UG_BLOCK_M * kCtaGroup) x UG_BLOCK_N
   int k_blocks;
   int group_m;           // tile rows per rasterisation group (L2 reuse)
+  int stages, copy_bufs; // shared-memory split of this launch: operand ring depth, broadcast staging buffers
   unsigned int *wave_sync;  // arrival counter of the soft per-tile rendezvous of the TMA producers (null: off)
   // fused B broadcast (multi-GPU, non-root ranks): column panel p of B (= n-block p) may be loaded
   // once b_ready[p] >= ready_target; the CTA's otherwise idle warp 3 pulls B from the root GPU.
@@ -91,9 +92,19 @@ struct UmmaCfg {
   static constexpr int kABytes = UG_BLOCK_M * UG_ROW_BYTES;         // 16 KiB
   static constexpr int kBBytes = kBRows * UG_ROW_BYTES;             // 16 / 32 KiB
   static constexpr int kStageBytes = kABytes + kBBytes;
+  // Shared memory is split at launch time between the operand ring and the staging buffers of the fused
+  // broadcast: a plain GEMM runs kStages stages and no staging; a launch that also copies B runs one stage
+  // less and kCopyBufs 16 KiB staging buffers -- an NVLink pull is a round trip of several microseconds
+  // when the remote GPU is busy, and with two boxes in flight per SM (4.7 MB per GPU) the copy was
+  // latency-bound at 635 GB/s on a link that carries 770.
   static constexpr int kStages = (CG == 2) ? 6 : 4;
+  static constexpr int kStagesCopying = (CG == 2) ? 5 : 3;
+  static constexpr int kCopyBufs = (CG == 2) ? 4 : 2;
+  static constexpr int kMaxStages = 8;         // barrier slots reserved per kind
   static constexpr int kCopyBufBytes = 16384;  // one 256 x 32 box of 16-bit B or 256 x 64 of int8 (broadcast staging)
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 1024 /*barriers*/ + 2 * kCopyBufBytes;
+  static constexpr int smem_bytes(int stages, int bufs) { return stages * kStageBytes + 1024 /*align*/ + 1024 /*barriers*/ + bufs * kCopyBufBytes; }
+  static constexpr int kSmemBytes = smem_bytes(kStages, 0) > smem_bytes(kStagesCopying, kCopyBufs) ? smem_bytes(kStages, 0)
+                                                                                                    : smem_bytes(kStagesCopying, kCopyBufs);
 };
 
 // out-type helpers ---------------------------------------------------------------------------
@@ -168,7 +179,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                  const UmmaArgs p) {
   typedef UmmaCfg<CG> Cfg;
   typedef typename OutT<CT>::type OT;
-  constexpr int kStages = Cfg::kStages;
+  const int kStages = p.stages;          // operand ring depth of this launch (see UmmaCfg)
+  const int kBufs = p.copy_bufs;         // staging buffers of the broadcast warp
   constexpr int kElemBytes = (KIND == KIND_S8) ? 1 : 2;
   constexpr int kBlockK = UG_ROW_BYTES / kElemBytes;  // 64 or 128 elements
   constexpr int kMmaK = 32 / kElemBytes;              // 16 or 32 elements = 32 bytes
@@ -180,11 +192,11 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar_base = smem_base + kStages * Cfg::kStageBytes;
   // barrier layout (8 bytes each): full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem ptr
-  const uint32_t full_bar = bar_base, empty_bar = bar_base + 8 * kStages;
-  const uint32_t tfull_bar = bar_base + 16 * kStages, tempty_bar = tfull_bar + 16;
+  const uint32_t full_bar = bar_base, empty_bar = bar_base + 8 * Cfg::kMaxStages;
+  const uint32_t tfull_bar = bar_base + 16 * Cfg::kMaxStages, tempty_bar = tfull_bar + 16;
   const uint32_t tmem_slot = tempty_bar + 16;
-  const uint32_t copy_bar = bar_base + 512;           // 2 mbarriers for the broadcast staging buffers
-  const uint32_t copy_buf = bar_base + 1024;          // 2 x kCopyBufBytes, 1024-byte aligned
+  const uint32_t copy_bar = bar_base + 512;           // one mbarrier per broadcast staging buffer
+  const uint32_t copy_buf = bar_base + 1024;          // kBufs x kCopyBufBytes, 1024-byte aligned
   uint8_t *smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   volatile uint32_t *tmem_slot_ptr = reinterpret_cast<volatile uint32_t *>(smem_gen + (tmem_slot - smem_base));
 
@@ -204,8 +216,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     for (int a = 0; a < 2; a++) {
       mbar_init(tfull_bar + 8 * a, 1);
       mbar_init(tempty_bar + 8 * a, 4 * CG);  // one arrival per epilogue warp of every CTA in the pair
-      mbar_init(copy_bar + 8 * a, 1);
     }
+    for (int a = 0; a < kBufs; a++) mbar_init(copy_bar + 8 * a, 1);
     fence_barrier_init();
   }
   if (warp == 2) tmem_alloc<CG>(tmem_slot, kTmemCols);
@@ -372,7 +384,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         int panel, x, y;
         coords(i, panel, x, y);
         need_up(panel);
-        const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
+        const uint32_t b = (uint32_t)(i % kBufs);
+        const uint32_t bar = copy_bar + 8 * b, buf = copy_buf + Cfg::kCopyBufBytes * b;
         mbar_expect_tx(bar, kPullBytes);
         asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                      ::"r"(buf), "l"(&map_bsrc), "r"(bar), "r"(x), "r"(y) : "memory");
@@ -414,14 +427,17 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         pend_panel = panel;
       };
       int pend_arrive = -1;   // panel whose last store is committed but not yet confirmed
-      if (total > 0) issue(0);
-      if (total > 1) issue(1);
+      // kBufs - 1 loads are kept in flight: buffer (i - 1) mod kBufs is refilled (with box i - 1 + kBufs) as
+      // soon as the store that emptied it has read it, which is checked one store later so that this thread
+      // never sits waiting for the store it has just issued.
+      for (long long i = 0; i < total && i < kBufs - 1; i++) issue(i);
       for (long long i = 0; i < total; i++) {
         int panel, x, y;
         coords(i, panel, x, y);
-        const uint32_t bar = copy_bar + 8 * (uint32_t)(i & 1), buf = copy_buf + Cfg::kCopyBufBytes * (uint32_t)(i & 1);
-        if (i + 2 < total) need_up((int)((i + 2) / mine_per_panel));
-        mbar_wait(bar, (uint32_t)((i >> 1) & 1));
+        const uint32_t b = (uint32_t)(i % kBufs);
+        const uint32_t bar = copy_bar + 8 * b, buf = copy_buf + Cfg::kCopyBufBytes * b;
+        if (i + kBufs < total) need_up((int)((i + kBufs) / mine_per_panel));
+        mbar_wait(bar, (uint32_t)((i / kBufs) & 1));
         settle();
         asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                      ::"l"(&map_bdst), "r"(buf), "r"(x), "r"(y) : "memory");
@@ -443,9 +459,10 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (p.mc_mode == 2 && last_of_panel)
           last_of_panel = ((panel + 1) % p.mc_group) == 0 || panel + 1 == p.tiles_n;
         if (last_of_panel) pend_arrive = panel;
-        if (i + 2 < total) {
-          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // staging buffer free again
-          issue(i + 2);
+        if (i + kBufs - 1 < total) {
+          // every store but the one just committed has read its buffer: buffer (i - 1) mod kBufs is free
+          asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          issue(i + kBufs - 1);
         }
       }
       if (pend_arrive >= 0) {
@@ -593,6 +610,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   if (rc) return rc;
 
   UmmaArgs p;
+  p.stages = Cfg::kStages, p.copy_bufs = 0;
   p.M = M, p.N = N, p.K = K, p.ldc = ldc, p.C = C, p.alpha = alpha, p.beta = beta;
   p.tiles_m = (int)div_up(M, UG_BLOCK_M * CG);
   p.tiles_n = (int)div_up(N, UG_BLOCK_N);
@@ -705,7 +723,11 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(clusters * CG, 1, 1);
   cfg.blockDim = dim3(UG_THREADS, 1, 1);
-  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  // a launch that also copies B trades one operand stage for deeper staging (see UmmaCfg)
+  const bool copying = p.b_ready != nullptr;
+  p.stages = copying ? Cfg::kStagesCopying : Cfg::kStages;
+  p.copy_bufs = copying ? Cfg::kCopyBufs : 0;
+  cfg.dynamicSmemBytes = Cfg::smem_bytes(p.stages, p.copy_bufs);
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
