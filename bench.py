@@ -163,7 +163,7 @@ def _gen_float(torch, shape, kind, dtype, seed):
     return (torch.rand(shape, device="cuda", generator=g, dtype=torch.float32) * 2 - 1).to(dtype)
 
 
-def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="mcast", share=1, data="int"):
+def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="chain", share=1, data="int"):
     """Device-resident inputs for this rank's part of `name` plus the callables that run it.
     share: how many ranks the named size is divided over (world for strong scaling, 1 for weak).
     data: "int" = the reference's integer-valued fills; "float" = the second data set of SURVEY 8(d)."""
@@ -351,9 +351,11 @@ def make_workload(name, torch, ctx, world, rank, dist, peers=None, bcast="mcast"
         fused_C = C
         if world > 1 and peers is not None:
             # B lives on rank 0 only; every other rank's GEMM kernel gets it over NVLink while multiplying
-            routes, order = {}, [bcast] + [x for x in ("mcast", "chain", "star") if x != bcast]
+            # the chosen route first, then the two pull routes for comparison (the multicast route is measured
+            # only when asked for: --bcast mcast)
+            routes, order = {}, [bcast] + [x for x in ("chain", "star") if x != bcast]
             if world == 2:
-                order = [x for x in order if x != "chain"]      # with one receiver the chain is the star
+                order = [x for x in order if x == "star"] or ["star"]   # with one receiver every route is: pull from the root
             for mode in order:
                 try:
                     routes[mode] = peers.route(ctx, B, mode)
@@ -1018,10 +1020,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"],
                     help="N>1: exchange fused into the kernel over peer memory (default) or a NCCL collective after it")
-    ap.add_argument("--bcast", default="mcast", choices=["mcast", "chain", "star"],
-                    help="N>1 GEMMs, how B reaches the non-root ranks: mcast = the root stores it once to an NVSwitch "
-                         "multicast address (default; falls back to chain where there is no multicast), chain = rank r pulls "
-                         "from rank r-1's copy (every GPU sends B once), star = everybody pulls from the root")
+    ap.add_argument("--bcast", default="chain", choices=["chain", "star", "mcast"],
+                    help="N>1 GEMMs, how B reaches the non-root ranks: chain = rank r pulls from rank r-1's copy (every GPU "
+                         "sends B once; default), star = everybody pulls from the root, mcast = every receiver pulls 1/(N-1) "
+                         "of B from the root and stores it to an NVSwitch multicast address (measured slower: DESIGN.md 6)")
     ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
                     help="N>1.  strong (default): the named size is the whole job, each GPU takes 1/N of the elements "
                          "(vectors) or of the rows of A and C (GEMMs); weak: the named size PER GPU")

@@ -555,7 +555,7 @@ static EncodeTiledFn get_encode() {
 // harness calls the same GEMM on the same buffers over and over (warm-up + timed run, gemm.cpp:534-541).
 static int make_map(cuxb_ctx *ctx, CUtensorMap *map, const void *base, int ebytes, CUtensorMapDataType dt,
                     uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols, uint32_t box_rows,
-                    bool swizzle128 = true) {
+                    bool swizzle128 = true, bool must_be_local = false) {
   static_assert(sizeof(CUtensorMap) == 128, "descriptor size");
   {
     std::lock_guard<std::mutex> g(*ctx->tma_mu);
@@ -567,6 +567,20 @@ static int make_map(cuxb_ctx *ctx, CUtensorMap *map, const void *base, int ebyte
         return 0;
       }
     }
+  }
+  if (must_be_local) {
+    // The operand loads of the mainloop are issued by CTA pairs (cp.async.bulk.tensor ... cta_group::2, and
+    // any future cluster-multicast variant): TMA multicast loads here read only this GPU's memory, since on
+    // B200 a TMA multicast load from another GPU's memory hung the GPU.  Operands that live on a peer are
+    // brought over first (the fused broadcast does that with plain, per-CTA TMA loads) -- so a matrix given
+    // to the mainloop must be this device's own.  Checked once per descriptor (cache miss), not per launch.
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, base) == cudaSuccess && at.type == cudaMemoryTypeDevice)
+      CUXB_REQUIRE(at.device == ctx->device, CUXB_ERR_UNSUPPORTED,
+                   "GEMM operand %p lives on GPU %d, not on this context's GPU %d: operands of the tensor-core mainloop "
+                   "must be local (use the cuxb_mg_* entry points to bring B over)", base, at.device, ctx->device);
+    else
+      cudaGetLastError();
   }
   EncodeTiledFn enc = get_encode();
   CUXB_REQUIRE(enc != nullptr, CUXB_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled not available from the driver");
@@ -601,12 +615,12 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
                                  : (KIND == KIND_F16) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
                                                       : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   CUtensorMap ma, mb;
-  int rc = make_map(ctx, &ma, A, ebytes, dt, (uint64_t)M, (uint64_t)K, (uint64_t)lda, kBlockK, UG_BLOCK_M);
+  int rc = make_map(ctx, &ma, A, ebytes, dt, (uint64_t)M, (uint64_t)K, (uint64_t)lda, kBlockK, UG_BLOCK_M, true, true);
   if (rc) return rc;
   if (B_MN)
-    rc = make_map(ctx, &mb, B, ebytes, dt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, kBlockK);
+    rc = make_map(ctx, &mb, B, ebytes, dt, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, kBlockK, true, true);
   else
-    rc = make_map(ctx, &mb, B, ebytes, dt, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, kBlockK, Cfg::kBRows);
+    rc = make_map(ctx, &mb, B, ebytes, dt, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, kBlockK, Cfg::kBRows, true, true);
   if (rc) return rc;
 
   UmmaArgs p;

@@ -29,6 +29,13 @@ def test_reference_arm_json_line():
     cb = d["cpu_baseline"]
     assert cb["kind"] in ("reference", "port") and cb["cores"] >= 1 and cb["sample"] and cb["value"] == d["value"]
     assert "workload" in d["config"]
+    # the two arms print the same config for the same workload (the driver compares them) and the steps that were asked for
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert d["config"] == bench.describe("scan", 1, "strong")["config"] and d["metric"] == bench.describe("scan")["metric"]
+    assert d["steps"] == 2 and d["ms_per_step"] > 0
 
 
 def test_reference_arm_other_ranks_are_silent():
