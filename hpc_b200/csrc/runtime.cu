@@ -231,7 +231,7 @@ CUXB_API int cuxb_ipc_close(void *dptr) {
 }
 
 // Chained broadcast for the cuxb_mg_*gemm / cuxb_mg_linear_* calls of this context (see cuxb.h).
-CUXB_API int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *flags_up, const void *flags_down) {
+CUXB_API int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, void *flags_up, void *flags_down) {
   CUXB_REQUIRE(ctx != nullptr, CUXB_ERR_INVALID, "cuxb_mg_set_chain: null context");
   CUXB_REQUIRE(flags_local != nullptr || (flags_up == nullptr && flags_down == nullptr), CUXB_ERR_INVALID,
                "cuxb_mg_set_chain: flags_up / flags_down given without flags_local");

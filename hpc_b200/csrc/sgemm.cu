@@ -55,10 +55,11 @@ struct SgemmArgs {
   unsigned int *pull_ticket;  // arrival ticket, grows by the grid size per call
   unsigned int ticket_base, ready_target;
   int panels, n_copy;
-  // chained broadcast (cuxb_mg_set_chain; the protocol is described in umma_gemm.cu): peer-mapped
-  // flags, one epoch word per panel + the "all panels" word at index 4096
+  // chained broadcast (cuxb_mg_set_chain; the protocol is described in umma_gemm.cu): peer-mapped flags;
+  // a rank waits only on its own: word p written by the rank it pulls from, word 4096 by the rank that
+  // pulls from it, word 4097 (its count of completed calls) by itself
   unsigned int *chain_local;
-  const unsigned int *chain_up, *chain_down;
+  unsigned int *chain_up, *chain_down;
   unsigned int *done_ctr;
   unsigned int done_target;
   // NVSwitch multicast all-gather (cuxb_mg_set_multicast; the protocol is described in umma_gemm.cu):
@@ -121,14 +122,15 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
   if (p.chain_local != nullptr) {
     // our call epoch; nothing of the previous call may be overwritten before the next rank has read it
     if (tid == 0) {
-      epoch = sg_ld_acquire_sys(p.chain_local + 4096) + 1;
-      if (p.chain_down != nullptr) sg_wait_sys_reached(p.chain_down + 4096, epoch - 1);
+      epoch = sg_ld_acquire_sys(p.chain_local + 4097) + 1;     // our own count of completed calls
+      if (p.chain_down != nullptr) sg_wait_sys_reached(p.chain_local + 4096, epoch - 1);   // written by the rank that pulls from us
     }
     __syncthreads();
   }
   for (int pnl = 0; pnl < p.panels; pnl++) {
     if (p.chain_up != nullptr) {
-      if (tid == 0) sg_wait_sys_reached(p.chain_up + pnl, epoch);  // the upstream copy of this panel is complete
+      // the upstream copy of this panel is complete: the upstream rank wrote that into OUR flags (a local poll)
+      if (tid == 0) sg_wait_sys_reached(p.chain_local + pnl, epoch);
       __syncthreads();
     }
     const int r0 = pnl * kSgPullPanelK;
@@ -175,11 +177,16 @@ __device__ __noinline__ void sgemm_pull_b(const SgemmArgs &p, int c) {
                      ::"l"(p.mc_flags_mc + (p.mc_rank - 1) * kSgMcMaxGroups + pnl), "r"(p.mc_epoch) : "memory");
       }
       if (p.chain_local != nullptr && old + 1 == p.ready_target) {
-        // last copier of the panel: tell the rank that pulls from us, and count the panel
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_local + pnl), "r"(epoch) : "memory");
+        // last copier of the panel: tell the rank that pulls from us (a store into ITS flags), and count the panel
+        if (p.chain_down != nullptr)
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_down + pnl), "r"(epoch) : "memory");
         asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(p.done_ctr) : "memory");
-        if (old + 1 == p.done_target)
-          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_local + 4096), "r"(epoch) : "memory");
+        if (old + 1 == p.done_target) {
+          // every panel is here: count the call, and tell the rank we pulled from that we have read all of its copy
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_local + 4097), "r"(epoch) : "memory");
+          if (p.chain_up != nullptr)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.chain_up + 4096), "r"(epoch) : "memory");
+        }
       }
     }
   }
@@ -592,7 +599,7 @@ CUXB_API int cuxb_mg_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K,
   ctx->sg_pull_ticket_base += grid;                      // unsigned wrap-around is fine
   ctx->sg_pull_calls++;
   p.ready_target = ctx->sg_pull_calls * (unsigned int)p.n_copy;
-  p.chain_local = ctx->chain_local, p.chain_up = ctx->chain_up, p.chain_down = ctx->chain_down;
+  p.chain_local = ctx->chain_local, p.chain_up = const_cast<unsigned int *>(ctx->chain_up), p.chain_down = const_cast<unsigned int *>(ctx->chain_down);
   p.done_ctr = ctx->sg_pull + 4097, p.done_target = 0;
   if (ctx->chain_local != nullptr) {
     ctx->sg_pull_done_total += (unsigned int)p.panels;

@@ -57,11 +57,12 @@ struct UmmaArgs {
   unsigned int ready_target;
   // chained broadcast (cuxb_mg_set_chain): B is pulled from the previous rank's copy instead of the
   // root's, so every GPU's NVLink egress carries B once however many ranks there are.  Flags live in
-  // peer-mapped memory, one 32-bit word per panel holding the call epoch of the last completed fill,
-  // word kChainDone holding the epoch of the last call whose every panel was filled.
+  // peer-mapped memory and every rank WAITS only on its own: word p of a rank's flags is written by the
+  // rank it pulls from (the call epoch of that rank's last completed fill of panel p), word kChainDone by
+  // the rank that pulls from it (the last call that rank has read completely), word kChainEpoch by itself.
   unsigned int *chain_local;        // ours (null: no chain)
-  const unsigned int *chain_up;     // the rank we pull from (null: its B is complete -- the root)
-  const unsigned int *chain_down;   // the rank that pulls from us (null: nobody)
+  unsigned int *chain_up;           // the rank we pull from (null: its B is complete -- the root)
+  unsigned int *chain_down;         // the rank that pulls from us (null: nobody)
   unsigned int *done_ctr;           // local: panels published, grows by tiles_n per call
   unsigned int done_target;
   // NVSwitch multicast all-gather (cuxb_mg_set_multicast), world >= 3.  The root copies nothing.  Each of
@@ -84,7 +85,8 @@ struct UmmaArgs {
 };
 constexpr int kMcMaxGroups = 512;   // flag words per sending rank
 constexpr int kMcDoneBase = 4100;    // flag word kMcDoneBase + r: last call whose B rank r has read completely
-constexpr int kChainDone = 4096;
+constexpr int kChainDone = 4096;    // word written by the rank that pulls from us: the last call it has read completely
+constexpr int kChainEpoch = 4097;   // our own count of completed calls
 
 template <int CG>
 struct UmmaCfg {
@@ -357,12 +359,13 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (B_MN) x = panel * UG_BLOCK_N, y = c * kPullRows;
         else x = (c / kRowBoxes) * 256, y = panel * UG_BLOCK_N + (c % kRowBoxes) * kPullRows;
       };
-      // chain: our call epoch is one more than the last call completed on these flags.  Nothing of
-      // the previous call may be overwritten before the rank that pulls from us has read all of it.
+      // chain: our call epoch is one more than the last call we completed (our own counter word).  Nothing
+      // of the previous call may be overwritten before the rank that pulls from us has read all of it:
+      // it says so by writing the call's epoch into word kChainDone of OUR flags.
       unsigned int epoch = 0;
       if (p.chain_local != nullptr) {
-        epoch = ld_acquire_sys_u32(p.chain_local + kChainDone) + 1;
-        if (p.chain_down != nullptr) wait_sys_reached(p.chain_down + kChainDone, epoch - 1);
+        epoch = ld_acquire_sys_u32(p.chain_local + kChainEpoch) + 1;
+        if (p.chain_down != nullptr) wait_sys_reached(p.chain_local + kChainDone, epoch - 1);
       }
       if (p.mc_mode == 2) {
         // our stores land in EVERY rank's copy: nothing of the previous call may be overwritten before
@@ -371,19 +374,22 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           if (r != p.mc_rank) wait_sys_reached(p.mc_flags_local + kMcDoneBase + r, p.mc_epoch - 1);
       }
       int up_known = 0;  // panels of the upstream copy known to be complete
-      // The upstream flag lives on another GPU: a look at it is an NVLink round trip.  The copy loop
-      // therefore asks for the panel of box i + 2 BEFORE it sits down to wait for box i (whose own
-      // load is a round trip of the same length), so the two overlap.
-      auto need_up = [&](int panel) {
-        if (p.chain_up == nullptr || panel < up_known) return;
-        wait_sys_reached(p.chain_up + panel, epoch);
+      // Every flag a rank waits on lives in its OWN memory: the rank we pull from writes "panel p of call e
+      // is complete here" into word p of our flags (a store over NVLink that nobody waits for), so a look at
+      // it is a local load, not an NVLink round trip -- cheap enough to look before every load is issued and
+      // to go on with other work (the stores of boxes already in flight) when the panel is not there yet.
+      const bool has_up = p.chain_local != nullptr && p.chain_up != nullptr;
+      auto up_ready = [&](long long i) -> bool {
+        const int panel = (int)(i / mine_per_panel);
+        if (!has_up || panel < up_known) return true;
+        if ((int)(ld_acquire_sys_u32(p.chain_local + panel) - epoch) < 0) return false;
         asm volatile("fence.proxy.async;" ::: "memory");
         up_known = panel + 1;
+        return true;
       };
       auto issue = [&](long long i) {
         int panel, x, y;
         coords(i, panel, x, y);
-        need_up(panel);
         const uint32_t b = (uint32_t)(i % kBufs);
         const uint32_t bar = copy_bar + 8 * b, buf = copy_buf + Cfg::kCopyBufBytes * b;
         mbar_expect_tx(bar, kPullBytes);
@@ -399,9 +405,14 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       auto settle = [&]() {
         if (pend_panel < 0) return;
         if (pend_old + 1 == p.ready_target) {
-          st_release_sys_u32(p.chain_local + pend_panel, epoch);
-          if (atom_add_acq_rel_gpu(p.done_ctr, 1u) + 1 == p.done_target)
-            st_release_sys_u32(p.chain_local + kChainDone, epoch);
+          // the panel is complete here: tell the rank that pulls from us (a store into ITS flags)
+          if (p.chain_down != nullptr) st_release_sys_u32(p.chain_down + pend_panel, epoch);
+          if (atom_add_acq_rel_gpu(p.done_ctr, 1u) + 1 == p.done_target) {
+            // every panel is here, so we have read all we need from upstream: count the call, and tell
+            // the rank we pulled from that it may overwrite its copy
+            st_release_sys_u32(p.chain_local + kChainEpoch, epoch);
+            if (p.chain_up != nullptr) st_release_sys_u32(p.chain_up + kChainDone, epoch);
+          }
         }
         pend_panel = -1;
       };
@@ -427,16 +438,26 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         pend_panel = panel;
       };
       int pend_arrive = -1;   // panel whose last store is committed but not yet confirmed
-      // kBufs - 1 loads are kept in flight: buffer (i - 1) mod kBufs is refilled (with box i - 1 + kBufs) as
-      // soon as the store that emptied it has read it, which is checked one store later so that this thread
-      // never sits waiting for the store it has just issued.
-      for (long long i = 0; i < total && i < kBufs - 1; i++) issue(i);
+      // Up to kBufs boxes are in flight.  Box j uses buffer j mod kBufs, free again once the store of box
+      // j - kBufs has read it -- checked one store late (wait_group.read 1), so that this thread never sits
+      // waiting for the store it has just issued.  A load is issued only when its panel is complete upstream.
+      long long ni = 0;   // next box to issue
+      auto pump = [&](long long upto) {
+        while (ni < total && ni < upto && up_ready(ni)) issue(ni), ni++;
+      };
+      pump(kBufs);
       for (long long i = 0; i < total; i++) {
         int panel, x, y;
         coords(i, panel, x, y);
         const uint32_t b = (uint32_t)(i % kBufs);
         const uint32_t bar = copy_bar + 8 * b, buf = copy_buf + Cfg::kCopyBufBytes * b;
-        if (i + kBufs < total) need_up((int)((i + kBufs) / mine_per_panel));
+        if (ni <= i) {
+          // nothing of ours is in flight and the next panel is not complete upstream: now we do have to wait
+          const unsigned long long t0 = global_timer_ns_();
+          while (!up_ready(i))
+            if (global_timer_ns_() - t0 > 20000000000ull) __trap();
+          issue(i), ni = i + 1;
+        }
         mbar_wait(bar, (uint32_t)((i / kBufs) & 1));
         settle();
         asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
@@ -459,10 +480,10 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         if (p.mc_mode == 2 && last_of_panel)
           last_of_panel = ((panel + 1) % p.mc_group) == 0 || panel + 1 == p.tiles_n;
         if (last_of_panel) pend_arrive = panel;
-        if (i + kBufs - 1 < total) {
-          // every store but the one just committed has read its buffer: buffer (i - 1) mod kBufs is free
+        if (ni < total) {
+          // every store but the one just committed has read its buffer: buffers up to box i - 1's are free
           asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-          issue(i + kBufs - 1);
+          pump(i + kBufs);
         }
       }
       if (pend_arrive >= 0) {
@@ -707,7 +728,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
     p.b_ready = ctx->bcast_ready;
     p.ready_target = ctx->bcast_calls * (unsigned int)(clusters * CG);
     if (ctx->chain_local != nullptr) {
-      p.chain_local = ctx->chain_local, p.chain_up = ctx->chain_up, p.chain_down = ctx->chain_down;
+      p.chain_local = ctx->chain_local, p.chain_up = const_cast<unsigned int *>(ctx->chain_up), p.chain_down = const_cast<unsigned int *>(ctx->chain_down);
       p.done_ctr = ctx->bcast_ready + 4096;  // beyond the panel counters, never reset
       ctx->bcast_done_total += (unsigned int)p.tiles_n;
       p.done_target = ctx->bcast_done_total;

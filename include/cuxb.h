@@ -218,13 +218,16 @@ int cuxb_mg_linear_f16_f32acc(cuxb_ctx *ctx, void *stream, int M, int N, int K, 
  * from rank r - 1's b_local, rank 1 from the root), so that every GPU sends B once.  The flag buffers are
  * peer-mapped device memory of CUXB_MG_CHAIN_FLAGS_BYTES, zeroed once before the first call:
  * flags_local = this rank's; flags_up = that of the rank pulled from (NULL when that rank is the root: its
- * B is complete); flags_down = that of the rank that pulls from this one (NULL for the last rank).  A panel
- * is pulled once the upstream flags say it has landed there, and a call does not overwrite b_local before
- * the downstream rank has read all of the previous call's.  All non-root ranks must make the same
- * sequence of chained calls.  Host-side state only: takes effect for later calls; NULL, NULL, NULL
- * switches back to pulling from the root. */
+ * B is complete); flags_down = that of the rank that pulls from this one (NULL for the last rank).  Every
+ * rank WAITS only on its own flags and WRITES its neighbours': when a panel is complete here the kernel
+ * stores the call's number into the panel's word of flags_down, and when it has read all of a call's B it
+ * says so in flags_up -- so a wait is a local poll and never an NVLink round trip.  A panel is pulled once
+ * this rank's flags say it has landed upstream, and a call does not overwrite b_local before the downstream
+ * rank has read all of the previous call's.  All non-root ranks must make the same sequence of chained
+ * calls.  Host-side state only: takes effect for later calls; NULL, NULL, NULL switches back to pulling
+ * from the root. */
 #define CUXB_MG_CHAIN_FLAGS_BYTES 16640
-int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, const void *flags_up, const void *flags_down);
+int cuxb_mg_set_chain(cuxb_ctx *ctx, void *flags_local, void *flags_up, void *flags_down);
 /* NVSwitch multicast all-gather (3..8 ranks on a box whose GPUs sit behind an NVSwitch).  The chain above
  * needs world - 1 hops before the last rank sees the first panel, and every hop moves all of B.  Here the
  * root copies nothing and every other rank owns every (world-1)-th 16 KiB box of B (SGEMM: every

@@ -147,7 +147,7 @@ def test_pull_flags_survive_a_change_of_panel_count():
 def test_chained_broadcast_flag_protocol_sequential():
     """cuxb_mg_set_chain on one GPU: 'rank 1' pulls from the root's B, 'rank 2' from rank 1's copy.  The
     two launches run one after the other on the default stream, so nothing ever spins here -- this checks the
-    epoch arithmetic (panel flags, the all-panels word, the wait for the downstream rank's previous call)
+    epoch arithmetic (panel flags, the call counter, the downstream rank's "I have read it" word)
     over repeated calls and changing shapes; tests/test_gpu_multi.py runs a chain whose links really wait."""
     c1, c2 = capi.Context(0), capi.Context(0)
     nflag = capi.MG_CHAIN_FLAGS_BYTES // 4
@@ -174,9 +174,11 @@ def test_chained_broadcast_flag_protocol_sequential():
             assert torch.equal(B1, B) and torch.equal(B2, B)
             assert torch.equal(C1, want) and torch.equal(C2, want)
             panels = (N + 255) // 256
-            for f in (f1, f2):
-                fl = f.cpu().numpy()
-                assert np.all(fl[:panels] == epoch) and fl[4096] == epoch
+            # a rank's flags are written by its neighbours: panel words by the rank it pulls from, word 4096 by the
+            # rank that pulls from it; word 4097 is its own count of completed calls
+            a1, a2 = f1.cpu().numpy(), f2.cpu().numpy()
+            assert np.all(a2[:panels] == epoch) and a2[4097] == epoch and a2[4096] == 0      # rank 2: fed by rank 1, nobody downstream
+            assert np.all(a1[:panels] == 0) and a1[4096] == epoch and a1[4097] == epoch      # rank 1: fed by the root (no flags)
     # the same flags carry on through the fp32 and int8 kernels (one epoch sequence per chain)
     M, N, K = 384, 256, 272
     A = torch.randint(-2, 6, (M, K), device="cuda", generator=g).float()
@@ -191,7 +193,7 @@ def test_chained_broadcast_flag_protocol_sequential():
         sync()
         epoch += 1
         assert torch.equal(B2, B) and torch.equal(C1, want) and torch.equal(C2, want)
-        assert int(f1[4096]) == epoch and int(f2[4096]) == epoch and int(f2[2]) == epoch  # 3 k-panels
+        assert int(f1[4096]) == epoch and int(f1[4097]) == epoch and int(f2[4097]) == epoch and int(f2[2]) == epoch  # 3 k-panels
     A8 = torch.randint(-128, 128, (256, 512), device="cuda", generator=g, dtype=torch.int32).to(torch.int8)
     Bt = torch.randint(-128, 128, (600, 512), device="cuda", generator=g, dtype=torch.int32).to(torch.int8)
     want = torch.zeros((256, 600), dtype=torch.int32, device="cuda")
@@ -203,7 +205,7 @@ def test_chained_broadcast_flag_protocol_sequential():
     c2.mg_linear_s8(256, 600, 512, A8.data_ptr(), B1.data_ptr(), B2.data_ptr(), C2.data_ptr(), False)
     sync()
     assert torch.equal(B2, Bt) and torch.equal(C1, want) and torch.equal(C2, want)
-    assert int(f2[4096]) == epoch + 1
+    assert int(f2[4097]) == epoch + 1 and int(f1[4096]) == epoch + 1
     c1.mg_set_chain(0, 0, 0)
     c2.mg_set_chain(0, 0, 0)
     with pytest.raises(capi.CuxbError):
