@@ -451,6 +451,22 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         coords(i, panel, x, y);
         const uint32_t b = (uint32_t)(i % kBufs);
         const uint32_t bar = copy_bar + 8 * b, buf = copy_buf + Cfg::kCopyBufBytes * b;
+        // Announcements are normally made one box late (see below), which costs nothing while boxes keep
+        // coming.  If the next box is not there yet -- its load has not landed, or its panel is not even
+        // complete upstream -- this thread is about to idle, and a downstream rank may be waiting for
+        // exactly the panel whose announcement is pending: make it now.
+        if (pend_arrive >= 0 || pend_panel >= 0) {
+          if (ni <= i || !mbar_try_wait(bar, (uint32_t)((i / kBufs) & 1))) {
+            if (pend_arrive >= 0) {
+              asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+              asm volatile("fence.proxy.async;" ::: "memory");
+              __threadfence();
+              arrive(pend_arrive);
+              pend_arrive = -1;
+            }
+            settle();
+          }
+        }
         if (ni <= i) {
           // nothing of ours is in flight and the next panel is not complete upstream: now we do have to wait
           const unsigned long long t0 = global_timer_ns_();
