@@ -99,6 +99,10 @@ struct cuxb_ctx {
   unsigned int sg_pull_calls, sg_pull_ticket_base;
   int sg_pull_panels, sg_pull_ncopy;
   unsigned int sg_pull_done_total;
+  // Workspaces that a larger call has superseded.  They stay allocated until cuxb_ctx_destroy: a CUDA graph
+  // recorded earlier holds their address and must stay replayable (bounded: sizes double, so a handful).
+  void *retired[48];
+  int retired_n;
   // host-API staging
   void *stage[4];
   size_t stage_bytes[4];
@@ -121,4 +125,6 @@ struct cuxb_ctx {
 namespace cuxb {
 int ensure_device(cuxb_ctx *ctx);
 int stage_reserve(cuxb_ctx *ctx, int slot, size_t bytes, void **out);
+// keep a superseded workspace alive until the context is destroyed (frees at once only if the list is full)
+int retire_workspace(cuxb_ctx *ctx, void *p);
 }  // namespace cuxb

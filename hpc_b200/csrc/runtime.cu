@@ -27,6 +27,17 @@ int ensure_device(cuxb_ctx *ctx) {
   return 0;
 }
 
+int retire_workspace(cuxb_ctx *ctx, void *p) {
+  if (p == nullptr) return 0;
+  if (ctx->retired_n < (int)(sizeof(ctx->retired) / sizeof(ctx->retired[0]))) {
+    ctx->retired[ctx->retired_n++] = p;
+    return 0;
+  }
+  CUXB_CUDA(cudaDeviceSynchronize());   // list full (never in practice): fall back to freeing now
+  CUXB_CUDA(cudaFree(p));
+  return 0;
+}
+
 int stage_reserve(cuxb_ctx *ctx, int slot, size_t bytes, void **out) {
   if (ctx->stage_bytes[slot] < bytes) {
     if (ctx->stage[slot]) CUXB_CUDA(cudaFree(ctx->stage[slot]));
@@ -93,6 +104,7 @@ CUXB_API int cuxb_ctx_destroy(cuxb_ctx *c) {
   cudaDeviceSynchronize();
   if (c->red_partials) cudaFree(c->red_partials);
   if (c->red_ticket) cudaFree(c->red_ticket);
+  for (int i = 0; i < c->retired_n; i++) cudaFree(c->retired[i]);
   if (c->scan_state) cudaFree(c->scan_state);
   if (c->bcast_ready) cudaFree(c->bcast_ready);
   if (c->wave_sync) cudaFree(c->wave_sync);

@@ -468,8 +468,8 @@ static int scan_entry(const char *name, cuxb_ctx *ctx, void *stream, long long n
     long long cap = ctx->scan_state_tiles ? ctx->scan_state_tiles : 4096;
     while (cap < tiles) cap *= 2;
     if (ctx->scan_state) {
-      CUXB_CUDA(cudaDeviceSynchronize());
-      CUXB_CUDA(cudaFree(ctx->scan_state));
+      // not freed: a CUDA graph recorded with the smaller workspace must stay replayable
+      if ((rc = retire_workspace(ctx, ctx->scan_state))) return rc;
       ctx->scan_state = nullptr;
       ctx->scan_state_tiles = 0;
     }

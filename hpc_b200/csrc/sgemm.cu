@@ -514,8 +514,8 @@ CUXB_API int cuxb_sgemm_f32(cuxb_ctx *ctx, void *stream, int M, int N, int K, fl
     const size_t need = 4096 + (size_t)tiles * splits * 16 * SG_THREADS * sizeof(float4);
     if (ctx->sg_scratch_bytes < need) {
       if (ctx->sg_scratch) {
-        CUXB_CUDA(cudaDeviceSynchronize());
-        CUXB_CUDA(cudaFree(ctx->sg_scratch));
+        // not freed: a CUDA graph recorded with the smaller scratch must stay replayable
+        if ((rc = retire_workspace(ctx, ctx->sg_scratch))) return rc;
         ctx->sg_scratch = nullptr, ctx->sg_scratch_bytes = 0;
       }
       CUXB_CUDA(cudaMalloc(&ctx->sg_scratch, need));

@@ -40,10 +40,11 @@
  *     into a launch's arguments (the scan counts its epoch on the device, the
  *     reduction and split-K tickets reset themselves).  Call once outside the
  *     capture first, so that workspaces exist and nothing allocates while
- *     capturing.  A recorded launch holds the ADDRESS of the context's workspace: a later call on the same
- *     context that needs a larger one (a longer scan, a split-K GEMM with more tiles, larger *_host
- *     staging) frees and reallocates it, after which graphs recorded before must not be replayed --
- *     make the largest call first, or record again.  The multi-GPU reductions and scan (cuxb_mg_dot_f32 ...
+ *     capturing.  A recorded launch holds the ADDRESS of the context's workspace.  When a later call on the
+ *     same context needs a larger one (a longer scan, a split-K GEMM with more tiles) the old workspace is
+ *     kept allocated until cuxb_ctx_destroy, so graphs recorded before stay replayable
+ *     (tests/test_gpu_graphs.py); a replay and a direct call must still not overlap on the GPU when the
+ *     graph was recorded with the CURRENT workspace.  The multi-GPU reductions and scan (cuxb_mg_dot_f32 ...
  *     cuxb_mg_scan_i32) can be captured too: their exchange epoch is counted
  *     in the exchange buffer.  NOT capturable: the *_host entry points (they
  *     synchronise) and the fused-broadcast GEMMs (cuxb_mg_*gemm*,

@@ -92,3 +92,30 @@ def test_reductions_and_gemms_replay():
         want = oracle.gemm_f32(hA, hB, np.zeros((M, N), np.float32), 1.0, 0.0, order="ikj", threads=8)
         assert np.array_equal(host(C), want), rep
         assert np.array_equal(host(C16.view(torch.int16), np.uint16), oracle.hgemm_f16(hA16, hB16, threads=8)), rep
+
+
+def test_graph_recorded_before_a_workspace_grew_still_replays():
+    """A recorded scan holds the address of the context's tile-state workspace.  A later, larger scan on the
+    same context needs a bigger one; the old one is kept (not freed) until the context is destroyed, so the
+    graph recorded before stays valid."""
+    c = capi.Context(0)                      # fresh context: its scan workspace starts at 4096 tiles (2^25 elements)
+    n = 1_000_003
+    x = torch.zeros(n, dtype=torch.int32, device="cuda")
+    out = torch.zeros_like(x)
+    g = _capture(lambda st: c.scan_i32(n, x.data_ptr(), out.data_ptr(), 3, st))
+    big = (1 << 25) + 81920 + 5              # forces the workspace to grow
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(3)
+    xb = torch.randint(-2, 3, (big,), dtype=torch.int32, device="cuda", generator=gen)
+    ob = torch.empty_like(xb)
+    c.scan_i32(big, xb.data_ptr(), ob.data_ptr(), 0, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert torch.equal(ob[1:] - ob[:-1], xb[1:]) and int(ob[0]) == int(xb[0])
+    for rep in range(3):
+        h = dg.int_fill(n, -3, 3, np.int32, tag=900 + rep)
+        x.copy_(torch.from_numpy(h))
+        torch.cuda.synchronize()
+        g.replay()
+        torch.cuda.synchronize()
+        assert np.array_equal(host(out), oracle.scan_i32(h, seed=3)), rep
+    c.close()
