@@ -777,7 +777,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   // a launch that also copies B trades one operand stage for deeper staging (see UmmaCfg)
   const bool copying = p.b_ready != nullptr;
   p.stages = copying ? Cfg::kStagesCopying : Cfg::kStages;
-  p.copy_bufs = copying ? Cfg::kCopyBufs : 0;
+  p.copy_bufs = copying ? ((ctx->dbg_copy_bufs >= 2 && ctx->dbg_copy_bufs <= Cfg::kCopyBufs) ? ctx->dbg_copy_bufs : Cfg::kCopyBufs) : 0;
   cfg.dynamicSmemBytes = Cfg::smem_bytes(p.stages, p.copy_bufs);
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -835,12 +835,14 @@ using namespace cuxb;
 //   what 1: rasterisation group height (tile rows per L2 group), 0 = default, 1..64
 //   what 2: soft per-wave rendezvous of the TMA producers, value 1 = on (default), 0 = off
 //   what 3: multicast broadcast, panels per announcement, 0 = default (about eight announcements per call)
+//   what 4: staging buffers of the broadcast warp (boxes in flight per SM), 0 = default, 2..4
 CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (ctx == nullptr) return CUXB_ERR_INVALID;
   if (what == 0 && value >= 0 && value <= 2) return ctx->dbg_cta_group = value, 0;
   if (what == 1 && value >= 0 && value <= 64) return ctx->dbg_group_m = value, 0;
   if (what == 2) return ctx->dbg_no_wave_sync = value ? 0 : 1, 0;
   if (what == 3 && value >= 0 && value <= 64) return ctx->dbg_mc_group = value, 0;
+  if (what == 4 && value >= 0 && value <= 4) return ctx->dbg_copy_bufs = value, 0;
   return CUXB_ERR_INVALID;
 }
 
