@@ -50,6 +50,8 @@ struct UmmaArgs {
   int k_blocks;
   int group_m;           // tile rows per rasterisation group (L2 reuse)
   int stages, copy_bufs; // shared-memory split of this launch: operand ring depth, broadcast staging buffers
+  int n_halves;          // 256-column halves per tile: 1 = 256 x 256 tiles, two accumulators (epilogue of tile t overlaps the
+                         // mainloop of t+1); 2 = 256 x 512 tiles, one accumulator: A is loaded once per 512 columns
   unsigned int *wave_sync;  // arrival counter of the soft per-tile rendezvous of the TMA producers (null: off)
   // fused B broadcast (multi-GPU, non-root ranks): column panel p of B (= n-block p) may be loaded
   // once b_ready[p] >= ready_target; the CTA's otherwise idle warp 3 pulls B from the root GPU.
@@ -105,6 +107,9 @@ struct UmmaCfg {
   static constexpr int kMaxStages = 8;         // barrier slots reserved per kind
   static constexpr int kCopyBufBytes = 16384;  // one 256 x 32 box of 16-bit B or 256 x 64 of int8 (broadcast staging)
   static constexpr int smem_bytes(int stages, int bufs) { return stages * kStageBytes + 1024 /*align*/ + 1024 /*barriers*/ + bufs * kCopyBufBytes; }
+  // wide tiles (two 256-column halves of B per stage): kStagesWide stages of kABytes + 2 * kBBytes
+  static constexpr int kStagesWide = (CG == 2) ? 4 : 2;
+  static constexpr int smem_bytes_wide() { return kStagesWide * (kABytes + 2 * kBBytes) + 1024 + 1024; }
   static constexpr int kSmemBytes = smem_bytes(kStages, 0) > smem_bytes(kStagesCopying, kCopyBufs) ? smem_bytes(kStages, 0)
                                                                                                     : smem_bytes(kStagesCopying, kCopyBufs);
 };
@@ -192,7 +197,11 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + kStages * Cfg::kStageBytes;
+  const int NH = p.n_halves;                                    // 256-column halves per tile
+  const uint32_t stage_bytes = Cfg::kABytes + (uint32_t)NH * Cfg::kBBytes;
+  const int tile_n = UG_BLOCK_N * NH;
+  const int num_acc = NH == 2 ? 1 : 2;                          // TMEM accumulators in rotation
+  const uint32_t bar_base = smem_base + kStages * stage_bytes;
   // barrier layout (8 bytes each): full[kStages], empty[kStages], tmem_full[2], tmem_empty[2], tmem ptr
   const uint32_t full_bar = bar_base, empty_bar = bar_base + 8 * Cfg::kMaxStages;
   const uint32_t tfull_bar = bar_base + 16 * Cfg::kMaxStages, tempty_bar = tfull_bar + 16;
@@ -251,7 +260,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         int tm, tn;
         tile_coord(t, tm, tn);
         const int m0 = (tm * CG + (int)cta_rank) * UG_BLOCK_M;
-        const int n0 = tn * UG_BLOCK_N + (int)cta_rank * Cfg::kBRows;
+        const int n0 = tn * tile_n + (int)cta_rank * Cfg::kBRows;   // (+ 256 per half)
         if (p.wave_sync != nullptr && wave > 0 && is_leader) {
           // Soft rendezvous: the clusters of a wave share operand panels through the L2, which only
           // works while they read the same k-slices at about the same time.  Wait (a few microseconds
@@ -279,19 +288,22 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         }
         for (int kb = 0; kb < p.k_blocks; kb++) {
           mbar_wait(empty_bar + 8 * stage, phase ^ 1);
-          const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
-          const uint32_t sb = sa + Cfg::kABytes;
+          const uint32_t sa = smem_base + stage * stage_bytes;
           const uint32_t fb = full_bar + 8 * stage;
-          if (is_leader) mbar_expect_tx(fb, Cfg::kStageBytes * CG);
+          if (is_leader) mbar_expect_tx(fb, stage_bytes * CG);
           const int k0 = kb * kBlockK;
           tma_load_2d<CG>(sa, &map_a, fb, k0, m0);
-          if (B_MN) {
-            // B[K,N]: boxes of 64 n x kBlockK k, one per 64 columns
+          for (int h = 0; h < NH; h++) {
+            const uint32_t sb = sa + Cfg::kABytes + h * Cfg::kBBytes;
+            const int nh0 = n0 + h * UG_BLOCK_N;
+            if (B_MN) {
+              // B[K,N]: boxes of 64 n x kBlockK k, one per 64 columns
 #pragma unroll
-            for (int c = 0; c < Cfg::kBRows / 64; c++)
-              tma_load_2d<CG>(sb + c * (kBlockK * UG_ROW_BYTES), &map_b, fb, n0 + c * 64, k0);
-          } else {
-            tma_load_2d<CG>(sb, &map_b, fb, k0, n0);
+              for (int c = 0; c < Cfg::kBRows / 64; c++)
+                tma_load_2d<CG>(sb + c * (kBlockK * UG_ROW_BYTES), &map_b, fb, nh0 + c * 64, k0);
+            } else {
+              tma_load_2d<CG>(sb, &map_b, fb, k0, nh0);
+            }
           }
           if (++stage == kStages) stage = 0, phase ^= 1;
         }
@@ -312,22 +324,24 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         for (int kb = 0; kb < p.k_blocks; kb++) {
           mbar_wait(full_bar + 8 * stage, phase);
           tc_fence_after();
-          const uint32_t sa = smem_base + stage * Cfg::kStageBytes;
-          const uint32_t sb = sa + Cfg::kABytes;
+          const uint32_t sa = smem_base + stage * stage_bytes;
 #pragma unroll
           for (int k = 0; k < kMmaPerStage; k++) {
             // K-major: 32 bytes further along the 128-byte swizzled row;
             // MN-major: kMmaK k-rows of 128 bytes further down.
             const uint64_t adesc = make_smem_desc(sa + k * 32, 16, 1024);
-            const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (kMmaK * UG_ROW_BYTES), kBlockK * UG_ROW_BYTES, 1024)
-                                        : make_smem_desc(sb + k * 32, 16, 1024);
-            umma<CG, KIND>(tmem_d, adesc, bdesc, kIdesc, (kb | k) != 0);
+            for (int h = 0; h < NH; h++) {   // wide tiles: the same A slice against both halves of B
+              const uint32_t sb = sa + Cfg::kABytes + h * Cfg::kBBytes;
+              const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (kMmaK * UG_ROW_BYTES), kBlockK * UG_ROW_BYTES, 1024)
+                                          : make_smem_desc(sb + k * 32, 16, 1024);
+              umma<CG, KIND>(tmem_d + h * UG_BLOCK_N, adesc, bdesc, kIdesc, (kb | k) != 0);
+            }
           }
           umma_commit<CG>(empty_bar + 8 * stage);  // frees the smem slot (in both CTAs) when the MMAs retire
           if (++stage == kStages) stage = 0, phase ^= 1;
         }
         umma_commit<CG>(tfull_bar + 8 * acc);      // accumulator complete -> epilogue (both CTAs)
-        if (++acc == 2) acc = 0, acc_phase ^= 1;
+        if (++acc == num_acc) acc = 0, acc_phase ^= 1;
       }
     }
     __syncwarp();
@@ -525,16 +539,16 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       int tm, tn;
       tile_coord(t, tm, tn);
       const int row = (tm * CG + (int)cta_rank) * UG_BLOCK_M + q * 32 + lane;
-      const int n0 = tn * UG_BLOCK_N;
+      const int n0 = tn * tile_n;
       mbar_wait(tfull_bar + 8 * acc, acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * UG_BLOCK_N;
 #pragma unroll 1
-      for (int cb = 0; cb < UG_BLOCK_N / 32; cb++) {
+      for (int cb = 0; cb < tile_n / 32; cb++) {
         uint32_t v[32];
         tmem_ld32(taddr + cb * 32, v);
         tmem_ld_wait();
-        if (cb == UG_BLOCK_N / 32 - 1) {
+        if (cb == tile_n / 32 - 1) {
           // every word of this accumulator is now in registers: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
@@ -553,7 +567,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           }
         }
       }
-      if (++acc == 2) acc = 0, acc_phase ^= 1;
+      if (++acc == num_acc) acc = 0, acc_phase ^= 1;
     }
   }
 
@@ -664,7 +678,24 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   p.stages = Cfg::kStages, p.copy_bufs = 0;
   p.M = M, p.N = N, p.K = K, p.ldc = ldc, p.C = C, p.alpha = alpha, p.beta = beta;
   p.tiles_m = (int)div_up(M, UG_BLOCK_M * CG);
-  p.tiles_n = (int)div_up(N, UG_BLOCK_N);
+  // 256 x 512 tiles (see UmmaArgs::n_halves): CTA pairs only, and not in launches that also copy B
+  // A wide tile reads A once per 512 columns -- a quarter less shared-memory fill per flop, which on this
+  // power-capped part is clock: +10-16 % on long fp16 problems (16384^3: 1630 -> 1820 TFLOP/s in the same
+  // process) -- but it owns all of TMEM, so its epilogue is not hidden behind the next tile's mainloop, and
+  // it halves the number of tiles the waves are cut from.  Cost model fitted to tools/wide_sweep.py (units of
+  // one k-block of one 256-column half): narrow = waves_n * kb, wide = 2 * waves_w * (0.88 * kb + e), with
+  // e = 5.5 for 16-bit outputs and 12 for the int32 output of the int8 linear.
+  int nh = 1;
+  if (CG == 2 && b_pull_from == nullptr && mc_role == 0) {
+    const long long cl = ctx->sm_count / CG;
+    const long long kb = div_up(K, kBlockK), tm = div_up(M, UG_BLOCK_M * CG);
+    const double t_narrow = (double)div_up(tm * div_up(N, UG_BLOCK_N), cl) * (double)kb;
+    const double t_wide = 2.0 * (double)div_up(tm * div_up(N, 2 * UG_BLOCK_N), cl) * (0.88 * (double)kb + (KIND == KIND_S8 ? 12.0 : 5.5));
+    const bool pays = t_wide < 0.98 * t_narrow;
+    if (ctx->dbg_wide == 2 || (ctx->dbg_wide == 0 && pays)) nh = 2;
+  }
+  p.n_halves = nh;
+  p.tiles_n = (int)div_up(N, UG_BLOCK_N * nh);
   p.k_blocks = (int)div_up(K, kBlockK);
   p.group_m = ctx->dbg_group_m > 0 ? ctx->dbg_group_m : UG_GROUP_M;
   p.wave_sync = nullptr;
@@ -779,6 +810,10 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   p.stages = copying ? Cfg::kStagesCopying : Cfg::kStages;
   p.copy_bufs = copying ? ((ctx->dbg_copy_bufs >= 2 && ctx->dbg_copy_bufs <= Cfg::kCopyBufs) ? ctx->dbg_copy_bufs : Cfg::kCopyBufs) : 0;
   cfg.dynamicSmemBytes = Cfg::smem_bytes(p.stages, p.copy_bufs);
+  if (nh == 2) {
+    p.stages = Cfg::kStagesWide, p.copy_bufs = 0;
+    cfg.dynamicSmemBytes = Cfg::smem_bytes_wide();
+  }
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -836,6 +871,7 @@ using namespace cuxb;
 //   what 2: soft per-wave rendezvous of the TMA producers, value 1 = on (default), 0 = off
 //   what 3: multicast broadcast, panels per announcement, 0 = default (about eight announcements per call)
 //   what 4: staging buffers of the broadcast warp (boxes in flight per SM), 0 = default, 2..4
+//   what 5: tile width, 0 = default, 1 = 256 x 256 tiles, 2 = 256 x 512 tiles
 CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (ctx == nullptr) return CUXB_ERR_INVALID;
   if (what == 0 && value >= 0 && value <= 2) return ctx->dbg_cta_group = value, 0;
@@ -843,6 +879,7 @@ CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (what == 2) return ctx->dbg_no_wave_sync = value ? 0 : 1, 0;
   if (what == 3 && value >= 0 && value <= 64) return ctx->dbg_mc_group = value, 0;
   if (what == 4 && value >= 0 && value <= 4) return ctx->dbg_copy_bufs = value, 0;
+  if (what == 5 && value >= 0 && value <= 2) return ctx->dbg_wide = value, 0;
   return CUXB_ERR_INVALID;
 }
 

@@ -429,3 +429,38 @@ def test_sgemm_split_k_shapes(shape):
     want = oracle.gemm_f32(Af, Bf, C, 1.0, 0.0, order="ikj", threads=8)
     assert np.max(np.abs(got - want)) <= 2 * K * EPS
     assert np.array_equal(got, run_sgemm(Af, Bf, C, 1.0, 0.0))  # deterministic: same bits every run
+
+
+# ------------------------------------------------------------------ wide (256 x 512) tiles
+@pytest.mark.parametrize("shape", [(256, 512, 64), (300, 520, 200), (512, 1544, 1024), (1024, 2304, 2000), (1, 8, 8)])
+def test_wide_tiles_bit_exact(shape):
+    """The tensor-core kernel can cut C into 256 x 512 tiles (one TMEM accumulator, A loaded once per 512 columns);
+    the library picks them by a cost model for long problems.  Forced here on small and ragged shapes: fp16 gemm
+    (B[K,N]), bf16 / int8 linear (Bt[N,K]) must give the oracle's bits exactly as the 256 x 256 tiles do."""
+    M, N, K = shape
+    c = ctx()
+    c.debug_set("wide_tiles", 2)
+    try:
+        A16 = oracle.f32_to_f16(dg.int_fill((M, K), -10, 9, tag=61))
+        B16 = oracle.f32_to_f16(dg.int_fill((K, N), -10, 9, tag=62))
+        C0 = oracle.f32_to_f16(dg.int_fill((M, N), -10, 9, tag=63))
+        got = run_hgemm(A16, B16, C0, 2.0, -1.0)
+        assert np.array_equal(got, oracle.hgemm_f16(A16, B16, C0, 2.0, -1.0, threads=8))
+        Ab = oracle.f32_to_bf16(dg.int_fill((M, K), -8, 8, tag=64))
+        Bb = oracle.f32_to_bf16(dg.int_fill((N, K), -8, 8, tag=65))
+        dA, dB = dev(Ab), dev(Bb)
+        dC = torch.zeros((M, N), dtype=torch.int16, device="cuda")
+        c.linear_bf16(M, N, K, dA.data_ptr(), dB.data_ptr(), dC.data_ptr(), capi.BFLOAT16)
+        sync()
+        assert np.array_equal(host(dC, np.uint16), oracle.linear_bf16(Ab, Bb, threads=8))
+        if N % 4 == 0:
+            K8 = (K + 15) // 16 * 16
+            A8 = dg.int_fill((M, K8), -128, 127, np.int8, tag=66)
+            B8 = dg.int_fill((N, K8), -128, 127, np.int8, tag=67)
+            dA, dB = dev(A8), dev(B8)
+            dC = torch.zeros((M, N), dtype=torch.int32, device="cuda")
+            c.linear_s8(M, N, K8, dA.data_ptr(), dB.data_ptr(), dC.data_ptr())
+            sync()
+            assert np.array_equal(host(dC), oracle.linear_s8(A8, B8, threads=8))
+    finally:
+        c.debug_set("wide_tiles", 0)
