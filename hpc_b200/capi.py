@@ -159,7 +159,7 @@ class Context:
 
     def debug_set(self, what, value):
         """Tuning / test hook of THIS context: what = "cta_group" | "group_m" | "wave_sync"."""
-        check(lib().cuxb_debug_ctx_set(self._h, {"cta_group": 0, "group_m": 1, "wave_sync": 2, "mc_group": 3, "copy_bufs": 4, "wide_tiles": 5}[what], int(value)),
+        check(lib().cuxb_debug_ctx_set(self._h, {"cta_group": 0, "group_m": 1, "wave_sync": 2, "mc_group": 3, "copy_bufs": 4, "wide_tiles": 5, "direct_epilogue": 6}[what], int(value)),
               "cuxb_debug_ctx_set")
 
     def close(self):

@@ -117,7 +117,7 @@ struct cuxb_ctx {
   int tma_cache_n;
   int tma_cache_next;
   // tuning / test hooks (cuxb_debug_ctx_set): per context, zero = library default
-  int dbg_cta_group, dbg_group_m, dbg_no_wave_sync, dbg_mc_group, dbg_copy_bufs, dbg_wide;
+  int dbg_cta_group, dbg_group_m, dbg_no_wave_sync, dbg_mc_group, dbg_copy_bufs, dbg_wide, dbg_epilogue;
   std::mutex *mu;      // serialises the *_host entry points (they share the staging buffers)
   std::mutex *tma_mu;  // guards the descriptor cache (taken inside kernels' entry points, never with mu's order reversed)
 };

@@ -50,6 +50,7 @@ struct UmmaArgs {
   int k_blocks;
   int group_m;           // tile rows per rasterisation group (L2 reuse)
   int stages, copy_bufs; // shared-memory split of this launch: operand ring depth, broadcast staging buffers
+  int tma_epilogue;      // 1: C leaves through shared memory and TMA stores (beta == 0, plain launches); 0: direct stores
   int n_halves;          // 256-column halves per tile: 1 = 256 x 256 tiles, two accumulators (epilogue of tile t overlaps the
                          // mainloop of t+1); 2 = 256 x 512 tiles, one accumulator: A is loaded once per 512 columns
   unsigned int *wave_sync;  // arrival counter of the soft per-tile rendezvous of the TMA producers (null: off)
@@ -110,8 +111,10 @@ struct UmmaCfg {
   // wide tiles (two 256-column halves of B per stage): kStagesWide stages of kABytes + 2 * kBBytes
   static constexpr int kStagesWide = (CG == 2) ? 4 : 2;
   static constexpr int smem_bytes_wide() { return kStagesWide * (kABytes + 2 * kBBytes) + 1024 + 1024; }
-  static constexpr int kSmemBytes = smem_bytes(kStages, 0) > smem_bytes(kStagesCopying, kCopyBufs) ? smem_bytes(kStages, 0)
-                                                                                                    : smem_bytes(kStagesCopying, kCopyBufs);
+  static constexpr int kEpiBytes = 4 * 8192;   // TMA-store epilogue: two 4 KiB units per epilogue warp (plain launches only)
+  static constexpr int kSmemBytes = smem_bytes(kStages, 0) + kEpiBytes > smem_bytes(kStagesCopying, kCopyBufs)
+                                        ? smem_bytes(kStages, 0) + kEpiBytes : smem_bytes(kStagesCopying, kCopyBufs);
+  static_assert(kSmemBytes <= 232448, "more shared memory than an sm_100 CTA can have");
 };
 
 // out-type helpers ---------------------------------------------------------------------------
@@ -183,7 +186,7 @@ template <int KIND, bool B_MN, int CT, int CG>
 __global__ void __launch_bounds__(UG_THREADS, 1)
 umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const __grid_constant__ CUtensorMap map_bsrc, const __grid_constant__ CUtensorMap map_bdst,
-                 const UmmaArgs p) {
+                 const __grid_constant__ CUtensorMap map_c, const UmmaArgs p) {
   typedef UmmaCfg<CG> Cfg;
   typedef typename OutT<CT>::type OT;
   const int kStages = p.stages;          // operand ring depth of this launch (see UmmaCfg)
@@ -535,6 +538,9 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     int acc = 0;
     uint32_t acc_phase = 0;
     OT *C = reinterpret_cast<OT *>(p.C);
+    const bool use_tma_epi = p.tma_epilogue != 0;
+    const uint32_t epi_buf = bar_base + 1024 + (uint32_t)(warp - 4) * 8192u;   // two 4 KiB units per epilogue warp
+    int unit_buf = 0;
     for (int t = cluster_id; t < total_tiles; t += num_clusters) {
       int tm, tn;
       tile_coord(t, tm, tn);
@@ -558,7 +564,52 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           }
         }
         const int col = n0 + cb * 32;
-        if (row < p.M && col < p.N) {
+        if (use_tma_epi) {
+          // C leaves through shared memory: every lane writes its row's 32 values of this chunk into a
+          // 32-row x 128-byte unit (128-byte swizzle: 16-byte piece j of row r sits at piece j ^ (r & 7), so the
+          // 32 lanes' STS.128 are conflict-free), and when a unit is full one lane hands it to the TMA, which
+          // writes 32 full 128-byte rows -- instead of every lane scattering 16-byte stores over 32 rows.
+          constexpr int kChunksPerUnit = (sizeof(OT) == 2) ? 2 : 1;   // 64 or 32 columns per unit
+          const int cu = cb % kChunksPerUnit;
+          const uint32_t ubuf = epi_buf + (uint32_t)(unit_buf * 4096);
+          if (cu == 0) {
+            // the store that last read this buffer (two units ago) must have finished reading it
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncwarp();
+          }
+          const uint32_t rowaddr = ubuf + (uint32_t)lane * 128u;
+          if constexpr (sizeof(OT) == 2) {
+            alignas(16) OT o[32];
+#pragma unroll
+            for (int c = 0; c < 32; c++) f32_to_out(__fmul_rn(p.alpha, __uint_as_float(v[c])), o[c]);
+            const uint4 *o4 = reinterpret_cast<const uint4 *>(o);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+              const uint32_t piece = (uint32_t)((cu * 4 + j) ^ (lane & 7));
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + piece * 16u), "r"(o4[j].x), "r"(o4[j].y), "r"(o4[j].z), "r"(o4[j].w) : "memory");
+            }
+          } else {
+            uint32_t o[32];
+#pragma unroll
+            for (int c = 0; c < 32; c++) o[c] = (KIND == KIND_S8) ? v[c] : __float_as_uint(__fmul_rn(p.alpha, __uint_as_float(v[c])));
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+              const uint32_t piece = (uint32_t)(j ^ (lane & 7));
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + piece * 16u), "r"(o[4 * j]), "r"(o[4 * j + 1]), "r"(o[4 * j + 2]), "r"(o[4 * j + 3]) : "memory");
+            }
+          }
+          if (cu == kChunksPerUnit - 1) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            const int ucol = col - cu * 32, urow = row - lane;
+            if (lane == 0 && urow < p.M && ucol < p.N) {   // (the TMA clips a unit that sticks out of C)
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                           ::"l"(&map_c), "r"(ubuf), "r"(ucol), "r"(urow) : "memory");
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            unit_buf ^= 1;
+          }
+        } else if (row < p.M && col < p.N) {
           OT *cp = C + (size_t)row * p.ldc + col;
 #pragma unroll
           for (int g = 0; g < 4; g++) {
@@ -569,6 +620,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       }
       if (++acc == num_acc) acc = 0, acc_phase ^= 1;
     }
+    if (use_tma_epi && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // C is written before the CTA leaves
   }
 
   // teardown
@@ -684,13 +736,14 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   // process) -- but it owns all of TMEM, so its epilogue is not hidden behind the next tile's mainloop, and
   // it halves the number of tiles the waves are cut from.  Cost model fitted to tools/wide_sweep.py (units of
   // one k-block of one 256-column half): narrow = waves_n * kb, wide = 2 * waves_w * (0.88 * kb + e), with
-  // e = 5.5 for 16-bit outputs and 12 for the int32 output of the int8 linear.
+  // e = 3 for 16-bit outputs and 5 for the int32 output of the int8 linear (with the TMA-store epilogue; the
+  // direct-store epilogue cost 5.5 and 12).
   int nh = 1;
   if (CG == 2 && b_pull_from == nullptr && mc_role == 0) {
     const long long cl = ctx->sm_count / CG;
     const long long kb = div_up(K, kBlockK), tm = div_up(M, UG_BLOCK_M * CG);
     const double t_narrow = (double)div_up(tm * div_up(N, UG_BLOCK_N), cl) * (double)kb;
-    const double t_wide = 2.0 * (double)div_up(tm * div_up(N, 2 * UG_BLOCK_N), cl) * (0.88 * (double)kb + (KIND == KIND_S8 ? 12.0 : 5.5));
+    const double t_wide = 2.0 * (double)div_up(tm * div_up(N, 2 * UG_BLOCK_N), cl) * (0.88 * (double)kb + (KIND == KIND_S8 ? 5.0 : 3.0));
     const bool pays = t_wide < 0.98 * t_narrow;
     if (ctx->dbg_wide == 2 || (ctx->dbg_wide == 0 && pays)) nh = 2;
   }
@@ -814,6 +867,21 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
     p.stages = Cfg::kStagesWide, p.copy_bufs = 0;
     cfg.dynamicSmemBytes = Cfg::smem_bytes_wide();
   }
+  // C through shared memory and TMA stores: when nothing has to be read from C and the launch does not copy B
+  // (a copying launch needs that shared memory for its staging buffers)
+  CUtensorMap mc_out = mb;
+  p.tma_epilogue = 0;
+  if (!copying && p.b_ready == nullptr && beta == 0.f && ctx->dbg_epilogue != 1) {
+    constexpr int cbytes = (CT == CUXB_FLOAT16 || CT == CUXB_BFLOAT16) ? 2 : 4;
+    const CUtensorMapDataType cdt = CT == CUXB_FLOAT16    ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                    : CT == CUXB_BFLOAT16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                    : CT == CUXB_FLOAT32  ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                                          : CU_TENSOR_MAP_DATA_TYPE_INT32;
+    rc = make_map(ctx, &mc_out, C, cbytes, cdt, (uint64_t)M, (uint64_t)N, (uint64_t)ldc, 128 / cbytes, 32, true, false);
+    if (rc) return rc;
+    p.tma_epilogue = 1;
+    cfg.dynamicSmemBytes += Cfg::kEpiBytes;
+  }
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -822,7 +890,7 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  CUXB_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, msrc, mdst, p));
+  CUXB_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, msrc, mdst, mc_out, p));
   g_launches.fetch_add(1);
   return 0;
 }
@@ -872,6 +940,7 @@ using namespace cuxb;
 //   what 3: multicast broadcast, panels per announcement, 0 = default (about eight announcements per call)
 //   what 4: staging buffers of the broadcast warp (boxes in flight per SM), 0 = default, 2..4
 //   what 5: tile width, 0 = default, 1 = 256 x 256 tiles, 2 = 256 x 512 tiles
+//   what 6: epilogue, 0 = default (through shared memory and TMA stores where possible), 1 = direct stores
 CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (ctx == nullptr) return CUXB_ERR_INVALID;
   if (what == 0 && value >= 0 && value <= 2) return ctx->dbg_cta_group = value, 0;
@@ -880,6 +949,7 @@ CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (what == 3 && value >= 0 && value <= 64) return ctx->dbg_mc_group = value, 0;
   if (what == 4 && value >= 0 && value <= 4) return ctx->dbg_copy_bufs = value, 0;
   if (what == 5 && value >= 0 && value <= 2) return ctx->dbg_wide = value, 0;
+  if (what == 6 && value >= 0 && value <= 1) return ctx->dbg_epilogue = value, 0;
   return CUXB_ERR_INVALID;
 }
 
