@@ -75,6 +75,7 @@ SIGNATURES = {
     "cuxb_mg_set_multicast": ([_vp, _i, _i, _vp, _vp, _vp], _i),
     "cuxb_enable_peer_access": ([_i, _i], _i),
     "cuxb_mg_create": ([_i, C.POINTER(_i), C.POINTER(_vp)], _i),
+    "cuxb_mg_init": ([_i, C.POINTER(_vp)], _i),
     "cuxb_mg_destroy": ([_vp], _i),
     "cuxb_mg_world": ([_vp], _i),
     "cuxb_mg_device": ([_vp, _i], _i),
@@ -110,6 +111,7 @@ SIGNATURES = {
     "cuxb_probe_fp32": ([_vp, _i, _i, C.POINTER(C.c_double)], _i),
     "cuxb_probe_tensor": ([_vp, _i, _i, _i, C.POINTER(C.c_double), C.POINTER(C.c_double)], _i),
     "cuxb_probe_nvlink": ([_vp, _i, _i, _i, C.c_size_t, _i, C.POINTER(C.c_double)], _i),
+    "cuxb_workspace_bytes": ([_vp, C.c_char_p, _ll, _ll, _ll, C.POINTER(C.c_size_t)], _i),
     "cuxb_kernel_occupancy": ([_vp, C.c_char_p, C.POINTER(_i), C.POINTER(C.c_double), C.POINTER(_i),
                                C.POINTER(_i)], _i),
 }

@@ -289,6 +289,40 @@ CUXB_API int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *activ
   return 0;
 }
 
+// Scratch a call would need from the context (beyond its inputs and outputs), so that a caller with a memory
+// budget can plan: see cuxb.h.  Pure host arithmetic; ctx may be NULL (a 148-SM B200 is assumed).
+namespace cuxb { int sgemm_pick_splits(int tiles, int K, int room); }
+CUXB_API int cuxb_workspace_bytes(const cuxb_ctx *ctx, const char *kernel, long long m_or_n, long long N, long long K,
+                                  size_t *bytes) {
+  CUXB_REQUIRE(kernel != nullptr && bytes != nullptr, CUXB_ERR_INVALID, "cuxb_workspace_bytes: null argument");
+  CUXB_REQUIRE(m_or_n >= 0 && N >= 0 && K >= 0, CUXB_ERR_INVALID, "cuxb_workspace_bytes: negative size");
+  const int sms = ctx ? ctx->sm_count : 148;
+  *bytes = 0;
+  if (!strcmp(kernel, "dot_f32") || !strcmp(kernel, "sum_f32") || !strcmp(kernel, "nrm2_f32") || !strcmp(kernel, "sum_i32")) {
+    *bytes = 0;   // block partials and the ticket are part of every context (kReduceMaxBlocks * 8 + 256 bytes)
+  } else if (!strcmp(kernel, "scan_i32") || !strcmp(kernel, "scan_f32")) {
+    // one 64-bit state word per tile of 8192 elements, capacity doubling from 4096 tiles, + 32 control words
+    long long tiles = div_up(m_or_n > 0 ? m_or_n : 1, kScanTileElems), cap = 4096;
+    CUXB_REQUIRE(tiles <= kScanMaxTiles, CUXB_ERR_TOO_LARGE, "cuxb_workspace_bytes: n beyond the scan's maximum");
+    while (cap < tiles) cap *= 2;
+    *bytes = (size_t)(cap + 32) * 8;
+  } else if (!strcmp(kernel, "sgemm_f32")) {
+    // split-K only: per-tile tickets + the parked accumulators of every split
+    const long long tiles = div_up(m_or_n, 128) * div_up(N, 128);
+    const int splits = tiles > 0 && tiles <= 1024 ? sgemm_pick_splits((int)tiles, (int)K, 2 * sms) : 1;
+    *bytes = splits > 1 ? 4096 + (size_t)tiles * splits * 16 * 256 * 16 : 0;
+  } else if (!strcmp(kernel, "hgemm_f16") || !strcmp(kernel, "gemm_bf16") || !strcmp(kernel, "linear_s8") ||
+             !strcmp(kernel, "linear_bf16") || !strcmp(kernel, "linear_f16")) {
+    // the soft wave rendezvous of long problems: one 256-byte counter block
+    const long long kb = div_up(K, !strcmp(kernel, "linear_s8") ? 128 : 64);
+    const long long tiles = div_up(m_or_n, 256) * div_up(N, 256);
+    *bytes = (tiles >= 16 * (sms / 2) && kb >= 128) ? 256 : 0;
+  } else {
+    CUXB_REQUIRE(false, CUXB_ERR_INVALID, "cuxb_workspace_bytes: unknown kernel '%s'", kernel);
+  }
+  return 0;
+}
+
 // test hook (not in cuxb.h): rows per chunk the host pipelines would use; kind 0 = fp32 sgemm, 1 = fp16
 // gemm (fp16 out), 2 = int8 linear.  Pure host arithmetic, callable without a GPU.
 CUXB_API int cuxb_debug_host_chunk_rows(int kind, int M, int N, int K, int sm_count) {

@@ -145,6 +145,9 @@ CUXB_API int cuxb_mg_create(int ndev, const int *devices, cuxb_mg **out) {
   return 0;
 }
 
+// SURVEY 8(b) names the constructor cuxb_mg_init(ndev, &mg): devices 0 .. ndev-1
+CUXB_API int cuxb_mg_init(int ndev, cuxb_mg **out) { return cuxb_mg_create(ndev, nullptr, out); }
+
 CUXB_API int cuxb_mg_destroy(cuxb_mg *mg) {
   if (!mg) return 0;
   for (int r = 0; r < mg->world; r++) {

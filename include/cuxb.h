@@ -270,6 +270,7 @@ int cuxb_enable_peer_access(int device, int peer_device);
  * one host thread per cuxb_mg.  The caller's current device is changed by these calls. */
 typedef struct cuxb_mg cuxb_mg;
 int cuxb_mg_create(int ndev, const int *devices, cuxb_mg **out);
+int cuxb_mg_init(int ndev, cuxb_mg **out);      /* = cuxb_mg_create(ndev, NULL, out) */
 int cuxb_mg_destroy(cuxb_mg *mg);
 int cuxb_mg_world(const cuxb_mg *mg);
 int cuxb_mg_device(const cuxb_mg *mg, int rank);
@@ -373,6 +374,14 @@ int cuxb_linear_s8_s32_host(cuxb_ctx *ctx, int M, int N, int K, const int8_t *A,
  * kernel: "dot_f32", "sum_f32", "nrm2_f32", "scan_i32", "sgemm_f32", "hgemm_f16". */
 int cuxb_kernel_occupancy(cuxb_ctx *ctx, const char *kernel, int *active_blocks_per_sm,
                           double *occupancy, int *threads_per_block, int *dynamic_smem_bytes);
+
+/* Scratch memory (device memory beyond the inputs and outputs) the context would hold after a call of this
+ * size, for callers that plan a memory budget: what cux leaves to cudaMalloc inside Array4D / the cuBLAS handle
+ * (0-frameworks/cux/include/operator/op_assistor.h:100-143).  kernel: "dot_f32", "sum_f32", "nrm2_f32", "sum_i32"
+ * (m_or_n = n; 0: their 16 KiB of partials belong to every context), "scan_i32", "scan_f32" (m_or_n = n),
+ * "sgemm_f32", "hgemm_f16", "gemm_bf16", "linear_s8", "linear_bf16", "linear_f16" (m_or_n = M, N, K).  The
+ * *_host entry points additionally stage their operands on the device.  Pure host arithmetic; ctx may be NULL. */
+int cuxb_workspace_bytes(const cuxb_ctx *ctx, const char *kernel, long long m_or_n, long long N, long long K, size_t *bytes);
 
 /* ---- measured ceilings of this GPU, for a harness that prints roofline fractions: the counterpart of the
  * reference's evaluation helpers (pocket-ai/eval/cuda/bandwidth_eval.hpp:257-300, timed device-to-device

@@ -96,3 +96,19 @@ def test_host_side_planning_arithmetic_without_a_gpu():
         per = L.cuxb_debug_host_chunk_rows(kind, M, N, K, sm)
         assert 0 < per <= M and (per % gran == 0 or per == M)
         assert 2 <= -(-M // per) <= 16
+
+
+def test_workspace_query_without_a_gpu():
+    """cuxb_workspace_bytes: the scratch a call would leave in the context -- pure host arithmetic, ctx may be NULL."""
+    import ctypes as C
+    L = capi.lib()
+    b = C.c_size_t()
+    q = lambda k, m, n=0, kk=0: (capi.check(L.cuxb_workspace_bytes(None, k.encode(), m, n, kk, C.byref(b)), "cuxb_workspace_bytes"), b.value)[1]
+    assert q("dot_f32", 1 << 28) == 0
+    assert q("scan_i32", 1 << 20) == (4096 + 32) * 8                 # the initial capacity covers 2^25 elements
+    assert q("scan_i32", 1 << 30) == ((1 << 17) + 32) * 8            # 2^30 / 8192 tiles
+    assert q("sgemm_f32", 8192, 8192, 8192) == 0                     # enough tiles: no split-K
+    sp = L.cuxb_debug_sgemm_splits(512, 576, 480, 148)
+    assert sp > 1 and q("sgemm_f32", 512, 576, 480) == 4096 + 4 * 5 * sp * 16 * 256 * 16
+    assert q("hgemm_f16", 16384, 16384, 16384) == 256 and q("hgemm_f16", 4096, 4096, 4096) == 0
+    assert L.cuxb_workspace_bytes(None, b"nope", 1, 1, 1, C.byref(b)) != 0
