@@ -30,6 +30,8 @@
 #include <cuda_fp16.h>
 #include <string.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "umma_ptx.cuh"
 
@@ -296,18 +298,24 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           if (is_leader) mbar_expect_tx(fb, stage_bytes * CG);
           const int k0 = kb * kBlockK;
           tma_load_2d<CG>(sa, &map_a, fb, k0, m0);
-          for (int h = 0; h < NH; h++) {
-            const uint32_t sb = sa + Cfg::kABytes + h * Cfg::kBBytes;
-            const int nh0 = n0 + h * UG_BLOCK_N;
-            if (B_MN) {
-              // B[K,N]: boxes of 64 n x kBlockK k, one per 64 columns
+          auto load_b = [&](auto width) {
+            constexpr int kHalves = decltype(width)::value;
 #pragma unroll
-              for (int c = 0; c < Cfg::kBRows / 64; c++)
-                tma_load_2d<CG>(sb + c * (kBlockK * UG_ROW_BYTES), &map_b, fb, nh0 + c * 64, k0);
-            } else {
-              tma_load_2d<CG>(sb, &map_b, fb, k0, nh0);
+            for (int h = 0; h < kHalves; h++) {
+              const uint32_t sb = sa + Cfg::kABytes + h * Cfg::kBBytes;
+              const int nh0 = n0 + h * UG_BLOCK_N;
+              if (B_MN) {
+                // B[K,N]: boxes of 64 n x kBlockK k, one per 64 columns
+#pragma unroll
+                for (int c = 0; c < Cfg::kBRows / 64; c++)
+                  tma_load_2d<CG>(sb + c * (kBlockK * UG_ROW_BYTES), &map_b, fb, nh0 + c * 64, k0);
+              } else {
+                tma_load_2d<CG>(sb, &map_b, fb, k0, nh0);
+              }
             }
-          }
+          };
+          if (NH == 1) load_b(std::integral_constant<int, 1>{});
+          else load_b(std::integral_constant<int, 2>{});
           if (++stage == kStages) stage = 0, phase ^= 1;
         }
       }
@@ -328,18 +336,26 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
           mbar_wait(full_bar + 8 * stage, phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * stage_bytes;
+          // (the tile width is a launch parameter, but this loop is the issue rate of the tensor pipe: it is
+          // written out for both widths with compile-time bounds -- a run-time inner loop cost narrow tiles 8 %)
+          auto issue_block = [&](auto width) {
+            constexpr int kHalves = decltype(width)::value;
 #pragma unroll
-          for (int k = 0; k < kMmaPerStage; k++) {
-            // K-major: 32 bytes further along the 128-byte swizzled row;
-            // MN-major: kMmaK k-rows of 128 bytes further down.
-            const uint64_t adesc = make_smem_desc(sa + k * 32, 16, 1024);
-            for (int h = 0; h < NH; h++) {   // wide tiles: the same A slice against both halves of B
-              const uint32_t sb = sa + Cfg::kABytes + h * Cfg::kBBytes;
-              const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (kMmaK * UG_ROW_BYTES), kBlockK * UG_ROW_BYTES, 1024)
-                                          : make_smem_desc(sb + k * 32, 16, 1024);
-              umma<CG, KIND>(tmem_d + h * UG_BLOCK_N, adesc, bdesc, kIdesc, (kb | k) != 0);
+            for (int k = 0; k < kMmaPerStage; k++) {
+              // K-major: 32 bytes further along the 128-byte swizzled row;
+              // MN-major: kMmaK k-rows of 128 bytes further down.
+              const uint64_t adesc = make_smem_desc(sa + k * 32, 16, 1024);
+#pragma unroll
+              for (int h = 0; h < kHalves; h++) {   // wide tiles: the same A slice against both halves of B
+                const uint32_t sb = sa + Cfg::kABytes + h * Cfg::kBBytes;
+                const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * (kMmaK * UG_ROW_BYTES), kBlockK * UG_ROW_BYTES, 1024)
+                                            : make_smem_desc(sb + k * 32, 16, 1024);
+                umma<CG, KIND>(tmem_d + h * UG_BLOCK_N, adesc, bdesc, kIdesc, (kb | k) != 0);
+              }
             }
-          }
+          };
+          if (NH == 1) issue_block(std::integral_constant<int, 1>{});
+          else issue_block(std::integral_constant<int, 2>{});
           umma_commit<CG>(empty_bar + 8 * stage);  // frees the smem slot (in both CTAs) when the MMAs retire
           if (++stage == kStages) stage = 0, phase ^= 1;
         }
@@ -468,21 +484,18 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         coords(i, panel, x, y);
         const uint32_t b = (uint32_t)(i % kBufs);
         const uint32_t bar = copy_bar + 8 * b, buf = copy_buf + Cfg::kCopyBufBytes * b;
-        // Announcements are normally made one box late (see below), which costs nothing while boxes keep
-        // coming.  If the next box is not there yet -- its load has not landed, or its panel is not even
-        // complete upstream -- this thread is about to idle, and a downstream rank may be waiting for
-        // exactly the panel whose announcement is pending: make it now.
-        if (pend_arrive >= 0 || pend_panel >= 0) {
-          if (ni <= i || !mbar_try_wait(bar, (uint32_t)((i / kBufs) & 1))) {
-            if (pend_arrive >= 0) {
-              asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-              asm volatile("fence.proxy.async;" ::: "memory");
-              __threadfence();
-              arrive(pend_arrive);
-              pend_arrive = -1;
-            }
-            settle();
+        if (ni <= i && (pend_arrive >= 0 || pend_panel >= 0)) {
+          // Announcements are normally made one box late (see below).  Here nothing of ours is in flight and
+          // we are about to wait for the upstream rank: a downstream rank may be waiting for exactly the
+          // panel whose announcement is pending, so make it first.
+          if (pend_arrive >= 0) {
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+            asm volatile("fence.proxy.async;" ::: "memory");
+            __threadfence();
+            arrive(pend_arrive);
+            pend_arrive = -1;
           }
+          settle();
         }
         if (ni <= i) {
           // nothing of ours is in flight and the next panel is not complete upstream: now we do have to wait
@@ -731,22 +744,13 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   p.M = M, p.N = N, p.K = K, p.ldc = ldc, p.C = C, p.alpha = alpha, p.beta = beta;
   p.tiles_m = (int)div_up(M, UG_BLOCK_M * CG);
   // 256 x 512 tiles (see UmmaArgs::n_halves): CTA pairs only, and not in launches that also copy B
-  // A wide tile reads A once per 512 columns -- a quarter less shared-memory fill per flop, which on this
-  // power-capped part is clock: +10-16 % on long fp16 problems (16384^3: 1630 -> 1820 TFLOP/s in the same
-  // process) -- but it owns all of TMEM, so its epilogue is not hidden behind the next tile's mainloop, and
-  // it halves the number of tiles the waves are cut from.  Cost model fitted to tools/wide_sweep.py (units of
-  // one k-block of one 256-column half): narrow = waves_n * kb, wide = 2 * waves_w * (0.88 * kb + e), with
-  // e = 3 for 16-bit outputs and 5 for the int32 output of the int8 linear (with the TMA-store epilogue; the
-  // direct-store epilogue cost 5.5 and 12).
+  // A wide tile reads A once per 512 columns (a quarter less shared-memory fill per flop), but it owns all of
+  // TMEM, so its epilogue is not hidden behind the next tile's mainloop, and it halves the number of tiles the
+  // waves are cut from.  Measured against the 256 x 256 tiles with both issue loops fully unrolled
+  // (tools/epilogue_sweep.py, 10 shapes, fp16 and int8): never faster by more than 2 % (16384^3), 5-25 % slower
+  // below that -- so it is a tuning hook (cuxb_debug_ctx_set what = 5), not a default.
   int nh = 1;
-  if (CG == 2 && b_pull_from == nullptr && mc_role == 0) {
-    const long long cl = ctx->sm_count / CG;
-    const long long kb = div_up(K, kBlockK), tm = div_up(M, UG_BLOCK_M * CG);
-    const double t_narrow = (double)div_up(tm * div_up(N, UG_BLOCK_N), cl) * (double)kb;
-    const double t_wide = 2.0 * (double)div_up(tm * div_up(N, 2 * UG_BLOCK_N), cl) * (0.88 * (double)kb + (KIND == KIND_S8 ? 5.0 : 3.0));
-    const bool pays = t_wide < 0.98 * t_narrow;
-    if (ctx->dbg_wide == 2 || (ctx->dbg_wide == 0 && pays)) nh = 2;
-  }
+  if (CG == 2 && b_pull_from == nullptr && mc_role == 0 && ctx->dbg_wide == 2) nh = 2;
   p.n_halves = nh;
   p.tiles_n = (int)div_up(N, UG_BLOCK_N * nh);
   p.k_blocks = (int)div_up(K, kBlockK);
@@ -871,7 +875,13 @@ static int launch_umma(cuxb_ctx *ctx, cudaStream_t st, int M, int N, int K, floa
   // (a copying launch needs that shared memory for its staging buffers)
   CUtensorMap mc_out = mb;
   p.tma_epilogue = 0;
-  if (!copying && p.b_ready == nullptr && beta == 0.f && ctx->dbg_epilogue != 1) {
+  // ... and when it pays: the staged epilogue is much cheaper per byte of C (no scattered 16-byte stores), but
+  // its shared-memory traffic competes with the operand feed of the tensor pipe.  4-byte outputs (int32, fp32):
+  // always (+4 ... +70 % across tools/epilogue_sweep.py's shapes); 2-byte outputs: up to K = 4096 (+1 ... +30 %);
+  // beyond that the mainloop dominates and the direct stores are as good or up to a few per cent better.
+  constexpr int kOutBytes = (CT == CUXB_FLOAT16 || CT == CUXB_BFLOAT16) ? 2 : 4;
+  const bool epi_pays = kOutBytes == 4 || p.k_blocks <= 64 || ctx->dbg_epilogue == 2;
+  if (!copying && p.b_ready == nullptr && beta == 0.f && ctx->dbg_epilogue != 1 && epi_pays) {
     constexpr int cbytes = (CT == CUXB_FLOAT16 || CT == CUXB_BFLOAT16) ? 2 : 4;
     const CUtensorMapDataType cdt = CT == CUXB_FLOAT16    ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
                                     : CT == CUXB_BFLOAT16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
@@ -940,7 +950,7 @@ using namespace cuxb;
 //   what 3: multicast broadcast, panels per announcement, 0 = default (about eight announcements per call)
 //   what 4: staging buffers of the broadcast warp (boxes in flight per SM), 0 = default, 2..4
 //   what 5: tile width, 0 = default, 1 = 256 x 256 tiles, 2 = 256 x 512 tiles
-//   what 6: epilogue, 0 = default (through shared memory and TMA stores where possible), 1 = direct stores
+//   what 6: epilogue, 0 = default (through shared memory and TMA stores where it pays), 1 = direct stores, 2 = staged wherever possible
 CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (ctx == nullptr) return CUXB_ERR_INVALID;
   if (what == 0 && value >= 0 && value <= 2) return ctx->dbg_cta_group = value, 0;
@@ -949,7 +959,7 @@ CUXB_API int cuxb_debug_ctx_set(cuxb_ctx *ctx, int what, int value) {
   if (what == 3 && value >= 0 && value <= 64) return ctx->dbg_mc_group = value, 0;
   if (what == 4 && value >= 0 && value <= 4) return ctx->dbg_copy_bufs = value, 0;
   if (what == 5 && value >= 0 && value <= 2) return ctx->dbg_wide = value, 0;
-  if (what == 6 && value >= 0 && value <= 1) return ctx->dbg_epilogue = value, 0;
+  if (what == 6 && value >= 0 && value <= 2) return ctx->dbg_epilogue = value, 0;
   return CUXB_ERR_INVALID;
 }
 

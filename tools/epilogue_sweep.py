@@ -28,7 +28,7 @@ for (M, N, K) in [(4096, 4096, 4096), (8192, 8192, 8192), (16384, 16384, 2048), 
     ref = {}
     for rep in range(3):
         for c in cfgs:
-            ctx.debug_set("wide_tiles", c[0]); ctx.debug_set("direct_epilogue", c[1])
+            ctx.debug_set("wide_tiles", c[0]); ctx.debug_set("direct_epilogue", 1 if c[1] else 2)   # 1 = direct stores, 2 = staged wherever possible
             r[("f16", c)].append(t(lambda: ctx.hgemm_f16(M, N8, K8, 1.0, A.data_ptr(), K8, B.data_ptr(), N8, 0.0, C.data_ptr(), N8, capi.FLOAT16, st())))
             r[("s8", c)].append(t(lambda: ctx.linear_s8(M, N8, K8, A8.data_ptr(), B8.data_ptr(), C8.data_ptr(), st())))
             if rep == 0:
