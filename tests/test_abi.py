@@ -112,3 +112,35 @@ def test_workspace_query_without_a_gpu():
     assert sp > 1 and q("sgemm_f32", 512, 576, 480) == 4096 + 4 * 5 * sp * 16 * 256 * 16
     assert q("hgemm_f16", 16384, 16384, 16384) == 256 and q("hgemm_f16", 4096, 4096, 4096) == 0
     assert L.cuxb_workspace_bytes(None, b"nope", 1, 1, 1, C.byref(b)) != 0
+
+
+def test_library_is_sm100a_tensor_code():
+    """The built library really is what DESIGN.md says: sm_100a cubins only, tcgen05 MMAs (UTCHMMA / UTCIMMA), TMEM
+    loads (LDTM), TMA loads and stores (UTMALDG / UTMASTG), packed FFMA2 in the SGEMM -- read from its SASS."""
+    import shutil
+    import subprocess
+    import sys
+    if shutil.which("cuobjdump") is None and not os.path.exists("/usr/local/cuda/bin/cuobjdump"):
+        pytest.skip("cuobjdump not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run([sys.executable, os.path.join(root, "tools", "sass_opcodes.py")], check=True, capture_output=True, timeout=300)
+    txt = open(os.path.join(root, "profiles", "sass_opcodes_r02.txt")).read()
+    assert "cubin architectures: sm_100a\n" in txt
+    for op in ("UTCHMMA.2CTA", "UTCIMMA.2CTA", "LDTM", "UTMALDG", "UTMASTG", "UBLKCP", "FFMA2"):
+        assert op in txt, op
+    total = txt.strip().splitlines()[-1]
+    assert total.startswith("# whole library:") and "UTCHMMA" in total and "FFMA2 2624" in total
+
+
+def test_bench_descriptions_are_stable_across_gpu_counts():
+    """The driver lines the per-N bench values up by `metric`; both arms print the same config."""
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    for name in bench.ALL:
+        metrics = {bench.describe(name, n, "strong")["metric"] for n in (1, 2, 4, 8)}
+        assert len(metrics) == 1, name
+        assert "1/8 of it per GPU" in bench.describe(name, 8, "strong")["config"]["workload"]
+        assert "per GPU" in bench.describe(name, 8, "weak")["config"]["workload"]
